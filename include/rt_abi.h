@@ -1,0 +1,150 @@
+/*
+ * include/rt_abi.h -- C ABI of the B200 render-loop library (librt_b200.so).
+ *
+ * This is the drop-in boundary for ONE path of kaitlyndlee/Raytracing-Programs:
+ *     void raycast(json_data_t *json_struct, PPMFormat photo_data)   (C/raycast.h:8,
+ *     body C/raycast.c:79-130, called once from main at C/raycast.c:57)
+ * and everything below it (iterative_shoot :315, calc_color :381, find_nearest_object
+ * :441, ray_intersect_{plane,sphere,quadric} :545/:576/:614, the attenuation / Phong
+ * helpers :666-758 and v3math.c).  The reference has no FFI layer; its "operator API"
+ * is that one function, so the entry points here are what a cgo/ctypes/JNI binding for
+ * the path would bind.  Plain C types only, no exceptions, every call returns 0 on
+ * success or a negative rt_status (text via rt_last_error()).
+ *
+ * There is NO CPU fallback: every rt_render* call fails with RT_ERR_NO_DEVICE when no
+ * sm_100-class GPU is present.
+ */
+#ifndef RT_ABI_H
+#define RT_ABI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+typedef enum rt_status {
+  RT_OK = 0,
+  RT_ERR_NO_DEVICE = -1,   /* no CUDA device / not initialised */
+  RT_ERR_CUDA = -2,        /* a CUDA runtime call failed */
+  RT_ERR_ARG = -3,         /* bad argument (NULL, non-positive size, unknown type) */
+  RT_ERR_NO_SCENE = -4,    /* rt_render* before rt_scene_upload */
+  RT_ERR_NCCL = -5,        /* NCCL missing or failed (only when n_gpus > 1) */
+  RT_ERR_OOM = -6
+} rt_status;
+
+/* shape_type_t / light_type_t of the reference (C/objects.h:4-13), same values. */
+enum { RT_SPHERE = 0, RT_PLANE = 1, RT_QUADRIC = 2 };
+enum { RT_POINT = 0, RT_SPOTLIGHT = 1 };
+
+/* One shape, in FILE ORDER (index = position in the reference's shapes list; the
+ * nearest-hit tie-break and the self-skip use it, C/raycast.c:450,456).
+ * Replaces shape_t (C/objects.h:15-48) without the union and the next pointer.
+ * params: sphere {radius}; plane {normal x,y,z}; quadric {a,b,c,d,e,f,g,h,i,j}. */
+typedef struct rt_shape {
+  int32_t type;
+  float diffuse[3];
+  float specular[3];
+  float position[3];      /* unused for quadrics (the reference leaves it uninitialised) */
+  float reflectivity;
+  float refractivity;
+  float ior;              /* carried for completeness; the live path never reads it */
+  float params[10];
+} rt_shape;
+
+/* Replaces light_t (C/objects.h:50-61). cos_theta is the host-side
+ * cos(theta) of C/objects.c:179; theta/cos_theta/a0/direction are read for spots only. */
+typedef struct rt_light {
+  int32_t type;
+  float position[3];
+  float color[3];
+  float radial[3];        /* radial-a0, a1, a2 */
+  float theta;
+  float cos_theta;
+  float a0;               /* angular-a0 */
+  float direction[3];
+} rt_light;
+
+/* Replaces json_data_t (C/parse.h:11-18) after the list->array copy of C/raycast.c:87-102. */
+typedef struct rt_scene {
+  float camera_width;
+  float camera_height;
+  int32_t num_shapes;
+  int32_t num_lights;
+  const rt_shape *shapes;
+  const rt_light *lights;
+} rt_scene;
+
+/* Counters of one render (summed over all GPUs used). "Rays" are the
+ * find_nearest_object calls the reference semantics make:
+ * shadow rays are counted even when the any-hit search ends early. "tests" are the
+ * intersection tests the kernels actually executed, split in origin-only ("o", shared
+ * by all rays leaving one hit point) and per-direction ("d") parts. */
+typedef struct rt_stats {
+  uint64_t pixels;
+  uint64_t rays_primary;
+  uint64_t rays_reflection;
+  uint64_t rays_shadow;
+  uint64_t hit_points;          /* shaded hits (levels 0..6) */
+  uint64_t sphere_tests_o, sphere_tests_d;
+  uint64_t plane_tests_o, plane_tests_d;
+  uint64_t quadric_tests_o, quadric_tests_d;
+  uint64_t kernel_launches;
+  double flops;                 /* algorithmic flops executed, SURVEY.md section 8a convention */
+  double ms_kernels;            /* device time of the render kernels (max over GPUs) */
+  double ms_gather;             /* band gather to GPU 0 */
+  double ms_total;              /* the whole call, host clock */
+} rt_stats;
+
+/* Initialise n_gpus devices (0 = all visible). Safe to call again after rt_shutdown. */
+int rt_init(int n_gpus);
+/* One-process-per-GPU launchers (torchrun): use exactly the device with this ordinal. */
+int rt_init_device(int ordinal);
+int rt_device_count(void);            /* devices in use, 0 before rt_init */
+void rt_shutdown(void);
+const char *rt_last_error(void);
+int rt_abi_version(void);
+
+/* Flatten to type-sorted SoA (+ original index) and upload to every device in use.
+ * Takes the place of the list->VLA copy at C/raycast.c:87-107. The scene is copied;
+ * the caller keeps ownership of its arrays. */
+int rt_scene_upload(const rt_scene *scene);
+
+/* The raycast() body (C/raycast.c:109-129): render W x H, rows interleaved in bands of
+ * rt band height over the GPUs in use, bands gathered to GPU 0 (NCCL when n_gpus > 1),
+ * then copied to the HOST buffer rgb_out (3*W*H bytes, row-major, row 0 = top, no
+ * padding: the pixmap of PPMFormat, C/ppm.h:6-12, with size_t instead of int sizes). */
+int rt_render(int width, int height, uint8_t *rgb_out, rt_stats *stats);
+
+/* Same render, result left in device memory of GPU 0 (inputs resident, no D2H):
+ * *dev_rgb_out receives a device pointer owned by the library, valid until the next
+ * rt_render* / rt_shutdown. */
+int rt_render_device(int width, int height, void **dev_rgb_out, rt_stats *stats);
+
+/* One-process-per-GPU mode (torchrun ranks): render only the bands of `rank` out of
+ * `nranks` on the current device 0 of this process into a library-owned device buffer
+ * holding this rank's rows back to back (band order). The caller gathers the rank
+ * buffers with its own collective and de-interleaves with rt_band_rows(). */
+int rt_render_rank(int width, int height, int rank, int nranks,
+                   void **dev_rows_out, size_t *nbytes, rt_stats *stats);
+
+/* De-interleave gathered rank buffers (rank r's rows start at dev_staging +
+ * rank_offsets[r], device memory of this process's device) into the row-major frame
+ * dev_frame (3*W*H bytes). What rank 0 runs after its gather collective. */
+int rt_assemble_device(int width, int height, int nranks, const void *dev_staging,
+                       const int64_t *rank_offsets, void *dev_frame);
+
+/* Row ownership helpers shared by library, host and tests: band b = rows
+ * [b*band_h, min((b+1)*band_h, H)) belongs to rank b % nranks. */
+int rt_band_height(void);                       /* env RT_BAND_ROWS, default 32 */
+int64_t rt_rank_num_rows(int height, int rank, int nranks);
+/* Fills rows_out[0..n) with the image row of each row of the rank buffer; returns n. */
+int64_t rt_rank_rows(int height, int rank, int nranks, int32_t *rows_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_ABI_H */

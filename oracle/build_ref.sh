@@ -1,0 +1,34 @@
+#!/bin/bash
+# oracle/build_ref.sh -- TEST INFRASTRUCTURE.
+# Builds the patched reference from the sources where they lie
+# under $RT_REF (default /root/reference). Outputs ONLY binaries into oracle/_ref/:
+#   raytrace_ref      the reference CLI (C/Makefile:4 flags + -ffp-contract=off), patches P1+P2
+#   raytrace_asis     the as-shipped CLI (P1 only, so it does not crash) -- reported, not graded
+#   libref.so         row-range harness (oracle/ref_harness.c) for tests and the CPU baseline
+# No reference source is copied into the repo: the patched raycast.c lives in a mktemp dir.
+set -euo pipefail
+HERE="$(cd "$(dirname "$0")" && pwd)"
+REF="${RT_REF:-/root/reference}/C"
+OUT="$HERE/_ref"
+if [ ! -f "$REF/raycast.c" ]; then
+  echo "build_ref.sh: $REF/raycast.c not found; keeping prebuilt oracle/_ref" >&2
+  exit 0
+fi
+mkdir -p "$OUT"
+TMP="$(mktemp -d /tmp/rtref.XXXXXX)"
+trap 'rm -rf "$TMP"' EXIT
+# P1: zero num_lights (C/raycast.c:44).  P2: reset next_nearest_object (before C/raycast.c:357).
+sed -e 's|^  json_struct->num_shapes = 0;$|  json_struct->num_shapes = 0; json_struct->num_lights = 0;|' \
+    -e 's|^      next_nearest_object_index = find_nearest_object(json_struct, &next_nearest_object, next_ray_orgin, $|      next_nearest_object = NULL;\n&|' \
+    "$REF/raycast.c" > "$TMP/raycast_patched.c"
+sed -e 's|^  json_struct->num_shapes = 0;$|  json_struct->num_shapes = 0; json_struct->num_lights = 0;|' \
+    "$REF/raycast.c" > "$TMP/raycast_p1.c"
+grep -q 'next_nearest_object = NULL;' "$TMP/raycast_patched.c" || { echo "P2 patch did not apply" >&2; exit 1; }
+grep -q 'num_lights = 0;' "$TMP/raycast_patched.c" || { echo "P1 patch did not apply" >&2; exit 1; }
+CFLAGS="-O3 -ffp-contract=off -w -I$REF"
+SUPPORT="$REF/v3math.c $REF/ppm.c $REF/parse.c $REF/objects.c"
+gcc $CFLAGS "$TMP/raycast_patched.c" $SUPPORT -o "$OUT/raytrace_ref" -lm
+gcc $CFLAGS "$TMP/raycast_p1.c" $SUPPORT -o "$OUT/raytrace_asis" -lm
+gcc $CFLAGS -fPIC -shared -DREF_RAYCAST_C="\"$TMP/raycast_patched.c\"" \
+    "$HERE/ref_harness.c" $SUPPORT -o "$OUT/libref.so" -lm -lpthread
+echo "built: $(ls "$OUT")"

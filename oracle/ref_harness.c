@@ -1,0 +1,158 @@
+/*
+ * oracle/ref_harness.c -- TEST INFRASTRUCTURE, not product code.
+ *
+ * Wraps the UNMODIFIED-but-patched reference render loop (C/raycast.c) so tests
+ * and bench.py's cpu_baseline / --impl reference leg can call it row by row.
+ * The reference sources are never copied into this repo: build_ref.sh streams
+ * /root/reference/C/raycast.c through sed (patch P2 of SURVEY.md section 8c:
+ * "next_nearest_object = NULL;" before C/raycast.c:357, as CUDA/raycast.cu:224
+ * does) into a temp file outside the repo and passes its path as REF_RAYCAST_C.
+ * Patch P1 (num_lights never initialised, C/raycast.c:41-44) is applied here by
+ * calloc()ing the json_data_t.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may load the
+ * resulting oracle/_ref/libref.so.
+ */
+#define main ref_main
+#include REF_RAYCAST_C
+#undef main
+
+#include <pthread.h>
+
+typedef struct ref_scene {
+  json_data_t js;
+  shape_t *shapes;
+  light_t *lights;
+} ref_scene;
+
+/* Parse with the reference parser (C/parse.c:13) and copy the linked lists to
+ * heap arrays the way raycast() does on its stack (C/raycast.c:87-107). */
+void *ref_scene_load(const char *path) {
+  FILE *f = fopen(path, "r");
+  if (!f) return NULL;
+  ref_scene *s = (ref_scene *)calloc(1, sizeof(ref_scene));
+  parse_json(f, &s->js);
+  fclose(f);
+  s->shapes = (shape_t *)calloc((size_t)s->js.num_shapes + 1, sizeof(shape_t));
+  s->lights = (light_t *)calloc((size_t)s->js.num_lights + 1, sizeof(light_t));
+  /* iterative walk: the reference's recursive free/append is O(n) stack deep */
+  shape_t *cs = s->js.shapes_list;
+  for (int i = 0; i < s->js.num_shapes; i++) { s->shapes[i] = *cs; shape_t *n = cs->next; free(cs); cs = n; }
+  light_t *cl = s->js.lights_list;
+  for (int i = 0; i < s->js.num_lights; i++) { s->lights[i] = *cl; light_t *n = cl->next; free(cl); cl = n; }
+  s->js.shapes_list = s->shapes;
+  s->js.lights_list = s->lights;
+  return s;
+}
+
+void ref_scene_free(void *h) {
+  ref_scene *s = (ref_scene *)h;
+  if (!s) return;
+  free(s->shapes); free(s->lights); free(s);
+}
+
+int ref_scene_num_shapes(void *h) { return ((ref_scene *)h)->js.num_shapes; }
+int ref_scene_num_lights(void *h) { return ((ref_scene *)h)->js.num_lights; }
+float ref_scene_cam_w(void *h) { return ((ref_scene *)h)->js.camera_width; }
+float ref_scene_cam_h(void *h) { return ((ref_scene *)h)->js.camera_height; }
+
+/* Raw struct dump so the clean-room parser can be compared field by field.
+ * out: per shape 20 floats {type, Kd[3], Ks[3], pos[3], refl, refr, ior, u[0..6]}
+ * u = first 7 union floats would lose quadric h,i,j, so we emit 10 union floats:
+ * total 23 floats per shape. */
+void ref_scene_dump_shapes(void *h, float *out) {
+  ref_scene *s = (ref_scene *)h;
+  for (int i = 0; i < s->js.num_shapes; i++) {
+    shape_t *p = &s->shapes[i];
+    float *o = out + (size_t)i * 23;
+    o[0] = (float)p->type;
+    for (int k = 0; k < 3; k++) { o[1 + k] = p->diffuse_color[k]; o[4 + k] = p->specular_color[k]; }
+    for (int k = 0; k < 3; k++) o[7 + k] = (p->type == QUADRIC) ? 0.f : p->position[k];
+    o[10] = p->reflectivity; o[11] = p->refractivity; o[12] = p->ior;
+    const float *u = &p->a; /* union base (C/objects.h:22-45) */
+    int nu = p->type == SPHERE ? 1 : (p->type == PLANE ? 3 : 10);
+    for (int k = 0; k < 10; k++) o[13 + k] = k < nu ? u[k] : 0.f;
+  }
+}
+
+/* per light 18 floats {type, pos[3], color[3], radial[3], theta, cos_theta, a0, dir[3], 0, 0} */
+void ref_scene_dump_lights(void *h, float *out) {
+  ref_scene *s = (ref_scene *)h;
+  for (int i = 0; i < s->js.num_lights; i++) {
+    light_t *p = &s->lights[i];
+    float *o = out + (size_t)i * 18;
+    int spot = p->type == SPOTLIGHT;
+    o[0] = (float)p->type;
+    for (int k = 0; k < 3; k++) { o[1 + k] = p->position[k]; o[4 + k] = p->color[k]; o[7 + k] = p->radial_coef[k]; }
+    o[10] = spot ? p->theta : 0.f; o[11] = spot ? p->cos_theta : 0.f; o[12] = spot ? p->a0 : 0.f;
+    for (int k = 0; k < 3; k++) o[13 + k] = spot ? p->direction[k] : 0.f;
+    o[16] = o[17] = 0.f;
+  }
+}
+
+/* Rows [y0,y1) of a W x H render, exactly the per-pixel body of raycast()
+ * (C/raycast.c:113-128), written to out[(y-y0)*W*3 ...]. */
+void ref_render_rows(void *h, int W, int H, int y0, int y1, uint8_t *out) {
+  ref_scene *s = (ref_scene *)h;
+  json_data_t *json_struct = &s->js;
+  int view_plane_center[3] = {0, 0, -1};
+  float ray_orgin[3] = {0, 0, 0};
+  float ray_direction[3];
+  float color[3];
+  uint8_t maxColor = 255;
+  float pixel_height = json_struct->camera_height / H;
+  float pixel_width = json_struct->camera_width / W;
+  uint8_t *pixel = out;
+  for (int y = y0; y < y1; y++) {
+    for (int x = 0; x < W; x++) {
+      ray_direction[0] = view_plane_center[0] - (json_struct->camera_width / 2.0) + pixel_width * (x + 0.5);
+      ray_direction[1] = view_plane_center[1] + (json_struct->camera_height / 2.0) - pixel_height * (y + 0.5);
+      ray_direction[2] = view_plane_center[2];
+      v3_normalize(ray_direction, ray_direction);
+      iterative_shoot(json_struct, ray_orgin, ray_direction, color, -1);
+      v3_scale(color, maxColor);
+      pixel[0] = ppm_clamp(color[0], 0, maxColor);
+      pixel[1] = ppm_clamp(color[1], 0, maxColor);
+      pixel[2] = ppm_clamp(color[2], 0, maxColor);
+      pixel += 3;
+    }
+  }
+}
+
+/* Multi-threaded row list render (rows[i] -> out + i*W*3): all host cores for
+ * the CPU baseline. The reference loop has no mutable globals, so it is
+ * re-entrant once the scene is read-only. */
+typedef struct { void *h; int W, H; const int *rows; int n; uint8_t *out; int tid, nthr; } ref_job;
+static void *ref_worker(void *a) {
+  ref_job *j = (ref_job *)a;
+  for (int i = j->tid; i < j->n; i += j->nthr)
+    ref_render_rows(j->h, j->W, j->H, j->rows[i], j->rows[i] + 1, j->out + (size_t)i * j->W * 3);
+  return NULL;
+}
+void ref_render_row_list(void *h, int W, int H, const int *rows, int n, uint8_t *out, int nthreads) {
+  if (nthreads < 1) nthreads = 1;
+  pthread_t th[256]; ref_job jb[256];
+  if (nthreads > 256) nthreads = 256;
+  for (int t = 0; t < nthreads; t++) {
+    jb[t] = (ref_job){h, W, H, rows, n, out, t, nthreads};
+    pthread_create(&th[t], NULL, ref_worker, &jb[t]);
+  }
+  for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
+}
+
+/* Known-answer entry points straight onto the reference functions. */
+int ref_isect_sphere(const float *o, const float *d, const float *centre, float r, float *t) {
+  shape_t s; memset(&s, 0, sizeof s); s.type = SPHERE; s.radius = r;
+  for (int k = 0; k < 3; k++) s.position[k] = centre[k];
+  return ray_intersect_sphere((float *)o, (float *)d, &s, t);
+}
+int ref_isect_plane(const float *o, const float *d, const float *pos, const float *n, float *t) {
+  shape_t s; memset(&s, 0, sizeof s); s.type = PLANE;
+  for (int k = 0; k < 3; k++) { s.position[k] = pos[k]; s.normal[k] = n[k]; }
+  return ray_intersect_plane((float *)o, (float *)d, &s, t);
+}
+int ref_isect_quadric(const float *o, const float *d, const float *q10, float *t) {
+  shape_t s; memset(&s, 0, sizeof s); s.type = QUADRIC;
+  float *u = &s.a; for (int k = 0; k < 10; k++) u[k] = q10[k];
+  return ray_intersect_quadric((float *)o, (float *)d, &s, t);
+}

@@ -1,0 +1,586 @@
+// csrc/rt_abi.cu -- implementation of include/rt_abi.h: scene flattening + upload,
+// tile scheduling of the wavefront kernels, multi-GPU band gather, statistics.
+// One host thread drives all GPUs of the process (asynchronous launches, one stream
+// per device).  NCCL is resolved with dlopen only when more than one GPU is in use.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <math.h>
+#include <nccl.h>   // types only; symbols come from dlopen("libnccl.so.2")
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/time.h>
+#include <vector>
+
+#include "rt_abi.h"
+#include "rt_kernels.cuh"
+
+#define RT_MAX_GPUS 8
+
+namespace {
+
+char g_err[512] = "";
+int set_err(int code, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return set_err(e_ == cudaErrorMemoryAllocation ? RT_ERR_OOM : RT_ERR_CUDA, "%s failed at %s:%d: %s", \
+                     #call, __FILE__, __LINE__, cudaGetErrorString(e_));                      \
+  } while (0)
+
+double now_ms() {
+  struct timeval tv;
+  gettimeofday(&tv, NULL);
+  return tv.tv_sec * 1e3 + tv.tv_usec / 1e3;
+}
+
+struct DeviceCtx {
+  int dev = -1;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+  int sm_count = 0;
+  // scene
+  void *scene_blob = nullptr;
+  DevScene sc{};
+  // per-tile working set
+  size_t tile_cap = 0;
+  float4 *acc = nullptr, *c0 = nullptr;
+  float4 *qbuf = nullptr;     // 6 * tile_cap float4: two queues x {r0,r1,r2}
+  int *qcount = nullptr;      // 8 ints: one count per wavefront level (+1 spare)
+  unsigned long long *counters = nullptr;
+  // output
+  uint8_t *rank_buf = nullptr; size_t rank_cap = 0;
+  uint8_t *staging = nullptr; size_t staging_cap = 0;   // device 0 only
+  uint8_t *frame = nullptr; size_t frame_cap = 0;       // device 0 only
+  int grid_primary = 0, grid_shade = 0, grid_fin = 0;
+};
+
+DeviceCtx g_dev[RT_MAX_GPUS];
+int g_ndev = 0;
+bool g_have_scene = false;
+int g_n_lights = 0, g_n_shapes = 0;
+
+// ---- NCCL through dlopen ---------------------------------------------------------
+struct NcclApi {
+  void *lib = nullptr;
+  ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+  ncclComm_t comms[RT_MAX_GPUS] = {};
+  bool ready = false;
+} g_nccl;
+
+int nccl_load(int ndev) {
+  if (g_nccl.ready) return RT_OK;
+  const char *names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char *n : names) { g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (g_nccl.lib) break; }
+  if (!g_nccl.lib) return set_err(RT_ERR_NCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+#define SYM(field, name)                                                          \
+  *(void **)(&g_nccl.field) = dlsym(g_nccl.lib, name);                            \
+  if (!g_nccl.field) return set_err(RT_ERR_NCCL, "libnccl lacks symbol %s", name)
+  SYM(CommInitAll, "ncclCommInitAll"); SYM(CommDestroy, "ncclCommDestroy");
+  SYM(GroupStart, "ncclGroupStart"); SYM(GroupEnd, "ncclGroupEnd");
+  SYM(Send, "ncclSend"); SYM(Recv, "ncclRecv"); SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+  int devs[RT_MAX_GPUS];
+  for (int i = 0; i < ndev; i++) devs[i] = g_dev[i].dev;
+  ncclResult_t r = g_nccl.CommInitAll(g_nccl.comms, ndev, devs);
+  if (r != ncclSuccess) return set_err(RT_ERR_NCCL, "ncclCommInitAll: %s", g_nccl.GetErrorString(r));
+  g_nccl.ready = true;
+  return RT_OK;
+}
+
+void nccl_unload() {
+  if (g_nccl.ready) for (int i = 0; i < g_ndev; i++) if (g_nccl.comms[i]) g_nccl.CommDestroy(g_nccl.comms[i]);
+  g_nccl = NcclApi();   // keep the library mapped: NCCL does not like dlclose
+}
+
+int band_rows() {
+  const char *e = getenv("RT_BAND_ROWS");
+  int v = e ? atoi(e) : 32;
+  return v > 0 ? v : 32;
+}
+size_t tile_pixels_cap() {
+  const char *e = getenv("RT_TILE_PIXELS");
+  long long v = e ? atoll(e) : (16ll << 20);
+  if (v < 1024) v = 1024;
+  if (v > (1ll << 30)) v = 1ll << 30;
+  return (size_t)v;
+}
+
+template <typename T>
+int dev_realloc(T *&p, size_t &cap, size_t need) {
+  if (need <= cap && p) return RT_OK;
+  if (p) { cudaFree(p); p = nullptr; cap = 0; }
+  CK(cudaMalloc((void **)&p, need));
+  cap = need;
+  return RT_OK;
+}
+
+void free_device(DeviceCtx &d) {
+  if (d.dev < 0) return;
+  cudaSetDevice(d.dev);
+  if (d.stream) cudaStreamSynchronize(d.stream);
+  cudaFree(d.scene_blob); cudaFree(d.acc); cudaFree(d.c0); cudaFree(d.qbuf); cudaFree(d.qcount);
+  cudaFree(d.counters); cudaFree(d.rank_buf); cudaFree(d.staging); cudaFree(d.frame);
+  if (d.ev0) cudaEventDestroy(d.ev0);
+  if (d.ev1) cudaEventDestroy(d.ev1);
+  if (d.ev2) cudaEventDestroy(d.ev2);
+  if (d.stream) cudaStreamDestroy(d.stream);
+  d = DeviceCtx();
+}
+
+}  // namespace
+
+// ==================================================================================
+extern "C" {
+
+int rt_abi_version(void) { return RT_ABI_VERSION; }
+const char *rt_last_error(void) { return g_err; }
+int rt_device_count(void) { return g_ndev; }
+int rt_band_height(void) { return band_rows(); }
+
+int64_t rt_rank_num_rows(int height, int rank, int nranks) {
+  if (height <= 0 || nranks <= 0 || rank < 0 || rank >= nranks) return 0;
+  const int bh = band_rows();
+  int64_t rows = 0;
+  for (int b = rank; (int64_t)b * bh < height; b += nranks) {
+    int64_t lo = (int64_t)b * bh, hi = lo + bh;
+    rows += (hi > height ? height : hi) - lo;
+  }
+  return rows;
+}
+
+int64_t rt_rank_rows(int height, int rank, int nranks, int32_t *rows_out) {
+  if (height <= 0 || nranks <= 0 || rank < 0 || rank >= nranks) return 0;
+  const int bh = band_rows();
+  int64_t n = 0;
+  for (int b = rank; (int64_t)b * bh < height; b += nranks)
+    for (int y = b * bh; y < (b + 1) * bh && y < height; y++) rows_out[n++] = y;
+  return n;
+}
+
+void rt_shutdown(void) {
+  nccl_unload();
+  for (int i = 0; i < RT_MAX_GPUS; i++) free_device(g_dev[i]);
+  g_ndev = 0;
+  g_have_scene = false;
+}
+
+int rt_init(int n_gpus) {
+  if (g_ndev) rt_shutdown();
+  int avail = 0;
+  cudaError_t e = cudaGetDeviceCount(&avail);
+  if (e != cudaSuccess || avail <= 0)
+    return set_err(RT_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU path",
+                   e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  if (n_gpus < 0 || n_gpus > RT_MAX_GPUS) return set_err(RT_ERR_ARG, "n_gpus=%d out of range", n_gpus);
+  int n = n_gpus == 0 ? (avail > RT_MAX_GPUS ? RT_MAX_GPUS : avail) : n_gpus;
+  if (n > avail) return set_err(RT_ERR_NO_DEVICE, "%d GPUs requested, %d visible", n, avail);
+  for (int i = 0; i < n; i++) {
+    DeviceCtx &d = g_dev[i];
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, i));
+    if (prop.major != 10)
+      return set_err(RT_ERR_NO_DEVICE, "device %d (%s, sm_%d%d) is not a Blackwell sm_100 part; kernels are sm_100a only",
+                     i, prop.name, prop.major, prop.minor);
+    CK(cudaSetDevice(i));
+    d.dev = i;
+    d.sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
+    CK(cudaMalloc((void **)&d.qcount, 8 * sizeof(int)));
+    CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
+  }
+  g_ndev = n;
+  if (n > 1) {
+    for (int i = 0; i < n; i++) {       // peer access lets NCCL use NVLink P2P
+      cudaSetDevice(i);
+      for (int j = 0; j < n; j++) if (i != j) { cudaDeviceEnablePeerAccess(j, 0); cudaGetLastError(); }
+    }
+    int r = nccl_load(n);
+    if (r != RT_OK) { int keep = r; char msg[512]; strncpy(msg, g_err, sizeof msg); rt_shutdown(); strncpy(g_err, msg, sizeof g_err); return keep; }
+  }
+  return RT_OK;
+}
+
+// ---- scene upload ------------------------------------------------------------------
+int rt_scene_upload(const rt_scene *scene) {
+  if (!g_ndev) return set_err(RT_ERR_NO_DEVICE, "rt_scene_upload before rt_init");
+  if (!scene || scene->num_shapes < 0 || scene->num_lights < 0 ||
+      (scene->num_shapes > 0 && !scene->shapes) || (scene->num_lights > 0 && !scene->lights))
+    return set_err(RT_ERR_ARG, "bad scene argument");
+  const int n = scene->num_shapes, nl = scene->num_lights;
+  std::vector<float4> sph, sph_prim, pln, quad, mat(2 * (size_t)n + 1), lights(4 * (size_t)nl + 1);
+  std::vector<int> sph_idx, pln_idx, quad_idx;
+  std::vector<int2> slot((size_t)n + 1);
+  for (int i = 0; i < n; i++) {
+    const rt_shape &s = scene->shapes[i];
+    // opacity, C/raycast.c:383: 1.0 - reflectivity - refractivity in double, stored float
+    const float opacity = (float)(1.0 - (double)s.reflectivity - (double)s.refractivity);
+    mat[2 * i] = make_float4(s.diffuse[0], s.diffuse[1], s.diffuse[2], s.reflectivity);
+    mat[2 * i + 1] = make_float4(s.specular[0], s.specular[1], s.specular[2], opacity);
+    if (s.type == RT_SPHERE) {
+      slot[i] = make_int2(0, (int)sph.size());
+      const float r = s.params[0];
+      sph.push_back(make_float4(s.position[0], s.position[1], s.position[2], r));
+      // primary rays start at exactly (0,0,0): temp = o - centre and c of C/raycast.c:581,585
+      volatile float t0 = 0.0f - s.position[0], t1 = 0.0f - s.position[1], t2 = 0.0f - s.position[2];
+      volatile float p0 = t0 * t0, p1 = t1 * t1, p2 = t2 * t2;
+      volatile float s01 = p0 + p1;
+      volatile float tt = s01 + p2;
+      sph_prim.push_back(make_float4(t0, t1, t2, fmaf(-r, r, tt)));
+      sph_idx.push_back(i);
+    } else if (s.type == RT_PLANE) {
+      slot[i] = make_int2(1, (int)pln_idx.size());
+      pln.push_back(make_float4(s.position[0], s.position[1], s.position[2], 0.f));
+      pln.push_back(make_float4(s.params[0], s.params[1], s.params[2], 0.f));
+      pln_idx.push_back(i);
+    } else if (s.type == RT_QUADRIC) {
+      slot[i] = make_int2(2, (int)quad_idx.size());
+      quad.push_back(make_float4(s.params[0], s.params[1], s.params[2], s.params[3]));
+      quad.push_back(make_float4(s.params[4], s.params[5], s.params[6], s.params[7]));
+      quad.push_back(make_float4(s.params[8], s.params[9], 0.f, 0.f));
+      quad_idx.push_back(i);
+    } else {
+      return set_err(RT_ERR_ARG, "shape %d has unknown type %d", i, s.type);
+    }
+  }
+  for (int l = 0; l < nl; l++) {
+    const rt_light &t = scene->lights[l];
+    if (t.type != RT_POINT && t.type != RT_SPOTLIGHT) return set_err(RT_ERR_ARG, "light %d has unknown type %d", l, t.type);
+    int ty = t.type; float tyf; memcpy(&tyf, &ty, 4);
+    lights[4 * l] = make_float4(t.position[0], t.position[1], t.position[2], tyf);
+    lights[4 * l + 1] = make_float4(t.color[0], t.color[1], t.color[2], t.cos_theta);
+    lights[4 * l + 2] = make_float4(t.radial[0], t.radial[1], t.radial[2], t.a0);
+    lights[4 * l + 3] = make_float4(t.direction[0], t.direction[1], t.direction[2], 0.f);
+  }
+  // one blob, 256-byte aligned sections
+  struct Sec { const void *src; size_t bytes; size_t off; };
+  Sec secs[10] = {
+      {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
+      {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
+      {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
+      {quad_idx.data(), quad_idx.size() * 4, 0}, {mat.data(), mat.size() * 16, 0},
+      {slot.data(), slot.size() * 8, 0},       {lights.data(), lights.size() * 16, 0}};
+  size_t total = 0;
+  for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
+  if (total == 0) total = 256;
+  std::vector<char> blob(total, 0);
+  for (auto &s : secs) if (s.bytes) memcpy(blob.data() + s.off, s.src, s.bytes);
+
+  for (int i = 0; i < g_ndev; i++) {
+    DeviceCtx &d = g_dev[i];
+    CK(cudaSetDevice(d.dev));
+    CK(cudaStreamSynchronize(d.stream));
+    if (d.scene_blob) { cudaFree(d.scene_blob); d.scene_blob = nullptr; }
+    CK(cudaMalloc(&d.scene_blob, total));
+    CK(cudaMemcpyAsync(d.scene_blob, blob.data(), total, cudaMemcpyHostToDevice, d.stream));
+    CK(cudaStreamSynchronize(d.stream));
+    char *b = (char *)d.scene_blob;
+    DevScene &sc = d.sc;
+    sc.n_shapes = n; sc.n_spheres = (int)sph.size(); sc.n_planes = (int)pln_idx.size();
+    sc.n_quadrics = (int)quad_idx.size(); sc.n_lights = nl;
+    sc.cam_w = scene->camera_width; sc.cam_h = scene->camera_height;
+    sc.sph = (const float4 *)(b + secs[0].off); sc.sph_prim = (const float4 *)(b + secs[1].off);
+    sc.sph_idx = (const int *)(b + secs[2].off); sc.pln = (const float4 *)(b + secs[3].off);
+    sc.pln_idx = (const int *)(b + secs[4].off); sc.quad = (const float4 *)(b + secs[5].off);
+    sc.quad_idx = (const int *)(b + secs[6].off); sc.mat = (const float4 *)(b + secs[7].off);
+    sc.slot = (const int2 *)(b + secs[8].off); sc.lights = (const float4 *)(b + secs[9].off);
+  }
+  g_have_scene = true;
+  g_n_lights = nl;
+  g_n_shapes = n;
+  return RT_OK;
+}
+
+}  // extern "C" (reopened below)
+
+namespace {
+
+template <int LB>
+int shade_grid(DeviceCtx &d) {
+  int per_sm = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_shade<LB>, 128, 0);
+  if (per_sm < 1) per_sm = 1;
+  return per_sm * d.sm_count;
+}
+
+template <int LB>
+void launch_shade(DeviceCtx &d, int grid, int level, HitQueue qin, HitQueue qout) {
+  k_shade<LB><<<grid, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters);
+}
+
+int pick_lb(int n_lights) {
+  const int c[5] = {1, 2, 4, 8, 16};
+  for (int v : c) if (n_lights <= v) return v;
+  return 16;
+}
+
+struct RankPlan { int64_t rows; size_t bytes; int launches; };
+
+// Enqueue the whole render of `rank`'s rows on device d (asynchronous).
+int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst, RankPlan *plan) {
+  CK(cudaSetDevice(d.dev));
+  const int bh = band_rows();
+  const int64_t rows = rt_rank_num_rows(H, rank, nranks);
+  const long long px_total = (long long)rows * W;
+  plan->rows = rows; plan->bytes = (size_t)px_total * 3; plan->launches = 0;
+  size_t tile = tile_pixels_cap();
+  if ((long long)tile > px_total) tile = (size_t)(px_total > 0 ? px_total : 1);
+  if (tile > d.tile_cap || !d.acc) {
+    cudaFree(d.acc); cudaFree(d.c0); cudaFree(d.qbuf); d.acc = d.c0 = d.qbuf = nullptr; d.tile_cap = 0;
+    CK(cudaMalloc((void **)&d.acc, tile * sizeof(float4)));
+    CK(cudaMalloc((void **)&d.c0, tile * sizeof(float4)));
+    CK(cudaMalloc((void **)&d.qbuf, 6 * tile * sizeof(float4)));
+    d.tile_cap = tile;
+  }
+  const int lb = pick_lb(d.sc.n_lights);
+  int per_sm = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_primary, 256, 0);
+  d.grid_primary = (per_sm > 0 ? per_sm : 1) * d.sm_count;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_finalize, 256, 0);
+  d.grid_fin = (per_sm > 0 ? per_sm : 1) * d.sm_count;
+  switch (lb) {
+    case 1: d.grid_shade = shade_grid<1>(d); break;
+    case 2: d.grid_shade = shade_grid<2>(d); break;
+    case 4: d.grid_shade = shade_grid<4>(d); break;
+    case 8: d.grid_shade = shade_grid<8>(d); break;
+    default: d.grid_shade = shade_grid<16>(d); break;
+  }
+  HitQueue q[2];
+  for (int k = 0; k < 2; k++) {
+    q[k].r0 = d.qbuf + (size_t)(3 * k) * d.tile_cap;
+    q[k].r1 = d.qbuf + (size_t)(3 * k + 1) * d.tile_cap;
+    q[k].r2 = d.qbuf + (size_t)(3 * k + 2) * d.tile_cap;
+    q[k].count = nullptr;
+  }
+  CK(cudaMemsetAsync(d.counters, 0, CT_COUNT * sizeof(unsigned long long), d.stream));
+  CK(cudaEventRecord(d.ev0, d.stream));
+  for (long long first = 0; first < px_total; first += (long long)tile) {
+    TileGeom tg;
+    tg.width = W; tg.height = H; tg.rank = rank; tg.nranks = nranks; tg.band_h = bh;
+    tg.first_px = first;
+    tg.n_px = (int)((px_total - first) < (long long)tile ? (px_total - first) : (long long)tile);
+    CK(cudaMemsetAsync(d.qcount, 0, 8 * sizeof(int), d.stream));
+    HitQueue q0 = q[0]; q0.count = d.qcount;
+    int gp = (tg.n_px + 255) / 256; if (gp > d.grid_primary) gp = d.grid_primary;
+    k_primary<<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, d.counters);
+    plan->launches++;
+    for (int level = 0; level < 7; level++) {
+      HitQueue qin = q[level & 1], qout = q[(level + 1) & 1];
+      qin.count = d.qcount + level; qout.count = d.qcount + level + 1;
+      switch (lb) {
+        case 1: launch_shade<1>(d, d.grid_shade, level, qin, qout); break;
+        case 2: launch_shade<2>(d, d.grid_shade, level, qin, qout); break;
+        case 4: launch_shade<4>(d, d.grid_shade, level, qin, qout); break;
+        case 8: launch_shade<8>(d, d.grid_shade, level, qin, qout); break;
+        default: launch_shade<16>(d, d.grid_shade, level, qin, qout); break;
+      }
+      plan->launches++;
+    }
+    int gf = (tg.n_px / 4 + 256) / 256; if (gf > d.grid_fin) gf = d.grid_fin;
+    k_finalize<<<gf, 256, 0, d.stream>>>(tg, d.acc, d.c0, dst);
+    plan->launches++;
+    CK(cudaGetLastError());
+  }
+  CK(cudaEventRecord(d.ev1, d.stream));
+  return RT_OK;
+}
+
+int collect_stats(int ndev, int W, int H, const RankPlan *plans, rt_stats *st, double ms_gather, double t0) {
+  rt_stats s;
+  memset(&s, 0, sizeof s);
+  s.pixels = (uint64_t)W * (uint64_t)H;
+  s.rays_primary = s.pixels;
+  double ms_k = 0;
+  for (int i = 0; i < ndev; i++) {
+    DeviceCtx &d = g_dev[i];
+    CK(cudaSetDevice(d.dev));
+    unsigned long long c[CT_COUNT];
+    CK(cudaMemcpy(c, d.counters, sizeof c, cudaMemcpyDeviceToHost));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, d.ev0, d.ev1));
+    if (ms > ms_k) ms_k = ms;
+    s.rays_reflection += c[CT_RAYS_REFLECTION]; s.rays_shadow += c[CT_RAYS_SHADOW];
+    s.hit_points += c[CT_HIT_POINTS];
+    s.sphere_tests_o += c[CT_SPH_O]; s.sphere_tests_d += c[CT_SPH_D];
+    s.plane_tests_o += c[CT_PLN_O]; s.plane_tests_d += c[CT_PLN_D];
+    s.quadric_tests_o += c[CT_QUAD_O]; s.quadric_tests_d += c[CT_QUAD_D];
+    s.kernel_launches += plans[i].launches;
+    // SURVEY.md section 8a flop convention
+    s.flops += 10.0 * c[CT_SPH_O] + 8.0 * c[CT_SPH_D] + 8.0 * c[CT_PLN_O] + 6.0 * c[CT_PLN_D] +
+               21.0 * c[CT_QUAD_O] + 37.0 * c[CT_QUAD_D] + 3.0 * c[CT_CANDIDATES] +
+               77.0 * c[CT_LIGHT_SAMPLES] + 12.0 * c[CT_RAYS_SHADOW] + 21.0 * c[CT_RAYS_REFLECTION] +
+               20.0 * c[CT_HIT_POINTS];
+  }
+  s.flops += 17.0 * (double)s.pixels;
+  s.ms_kernels = ms_k;
+  s.ms_gather = ms_gather;
+  s.ms_total = now_ms() - t0;
+  if (st) *st = s;
+  return RT_OK;
+}
+
+int check_render_args(int W, int H) {
+  if (!g_ndev) return set_err(RT_ERR_NO_DEVICE, "render before rt_init (no GPU initialised; there is no CPU path)");
+  if (!g_have_scene) return set_err(RT_ERR_NO_SCENE, "render before rt_scene_upload");
+  if (W <= 0 || H <= 0) return set_err(RT_ERR_ARG, "bad image size %dx%d", W, H);
+  if (W > (1 << 26) || H > (1 << 26)) return set_err(RT_ERR_ARG, "image too large: %dx%d", W, H);
+  return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_render_device(int W, int H, void **dev_rgb_out, rt_stats *stats) {
+  int r = check_render_args(W, H);
+  if (r != RT_OK) return r;
+  const double t0 = now_ms();
+  const int n = g_ndev;
+  RankPlan plans[RT_MAX_GPUS];
+  DeviceCtx &d0 = g_dev[0];
+  double ms_gather = 0;
+  if (n == 1) {
+    CK(cudaSetDevice(d0.dev));
+    size_t need = (size_t)W * H * 3 + 64;
+    if ((r = dev_realloc(d0.frame, d0.frame_cap, need)) != RT_OK) return r;
+    if ((r = enqueue_rank(d0, W, H, 0, 1, d0.frame, &plans[0])) != RT_OK) return r;
+    CK(cudaStreamSynchronize(d0.stream));
+  } else {
+    size_t off[RT_MAX_GPUS + 1];
+    off[0] = 0;
+    for (int i = 0; i < n; i++) {
+      size_t b = (size_t)rt_rank_num_rows(H, i, n) * W * 3;
+      off[i + 1] = off[i] + ((b + 255) & ~(size_t)255);
+    }
+    CK(cudaSetDevice(d0.dev));
+    if ((r = dev_realloc(d0.staging, d0.staging_cap, off[n] + 64)) != RT_OK) return r;
+    if ((r = dev_realloc(d0.frame, d0.frame_cap, (size_t)W * H * 3 + 64)) != RT_OK) return r;
+    for (int i = 0; i < n; i++) {
+      DeviceCtx &d = g_dev[i];
+      uint8_t *dst = d0.staging;   // rank 0 renders straight into its staging slot
+      if (i > 0) {
+        CK(cudaSetDevice(d.dev));
+        if ((r = dev_realloc(d.rank_buf, d.rank_cap, off[i + 1] - off[i] + 64)) != RT_OK) return r;
+        dst = d.rank_buf;
+      }
+      if ((r = enqueue_rank(d, W, H, i, n, dst, &plans[i])) != RT_OK) return r;
+    }
+    // band gather: every rank sends its rows to GPU 0 over NVLink (NCCL point-to-point)
+    ncclResult_t nr = g_nccl.GroupStart();
+    for (int i = 1; i < n && nr == ncclSuccess; i++) {
+      nr = g_nccl.Send(g_dev[i].rank_buf, plans[i].bytes, ncclUint8, 0, g_nccl.comms[i], g_dev[i].stream);
+      if (nr == ncclSuccess)
+        nr = g_nccl.Recv(d0.staging + off[i], plans[i].bytes, ncclUint8, i, g_nccl.comms[0], d0.stream);
+    }
+    ncclResult_t ne = g_nccl.GroupEnd();
+    if (nr != ncclSuccess || ne != ncclSuccess)
+      return set_err(RT_ERR_NCCL, "band gather failed: %s", g_nccl.GetErrorString(nr != ncclSuccess ? nr : ne));
+    CK(cudaSetDevice(d0.dev));
+    AssembleArgs a;
+    memset(&a, 0, sizeof a);
+    for (int i = 0; i < n; i++) a.rank_off[i] = (long long)off[i];
+    a.width = W; a.height = H; a.nranks = n; a.band_h = band_rows();
+    k_assemble<<<d0.sm_count * 8, 256, 0, d0.stream>>>(a, d0.staging, d0.frame);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(d0.ev2, d0.stream));
+    for (int i = 0; i < n; i++) { CK(cudaSetDevice(g_dev[i].dev)); CK(cudaStreamSynchronize(g_dev[i].stream)); }
+    CK(cudaSetDevice(d0.dev));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, d0.ev1, d0.ev2));
+    ms_gather = ms;
+    plans[0].launches += 1;
+  }
+  if (dev_rgb_out) *dev_rgb_out = d0.frame;
+  return collect_stats(n, W, H, plans, stats, ms_gather, t0);
+}
+
+int rt_render(int W, int H, uint8_t *rgb_out, rt_stats *stats) {
+  if (!rgb_out) return set_err(RT_ERR_ARG, "rgb_out is NULL");
+  const double t0 = now_ms();
+  void *frame = nullptr;
+  int r = rt_render_device(W, H, &frame, stats);
+  if (r != RT_OK) return r;
+  DeviceCtx &d0 = g_dev[0];
+  CK(cudaSetDevice(d0.dev));
+  CK(cudaMemcpyAsync(rgb_out, frame, (size_t)W * H * 3, cudaMemcpyDeviceToHost, d0.stream));
+  CK(cudaStreamSynchronize(d0.stream));
+  if (stats) stats->ms_total = now_ms() - t0;
+  return RT_OK;
+}
+
+int rt_render_rank(int W, int H, int rank, int nranks, void **dev_rows_out, size_t *nbytes, rt_stats *stats) {
+  int r = check_render_args(W, H);
+  if (r != RT_OK) return r;
+  if (nranks < 1 || rank < 0 || rank >= nranks) return set_err(RT_ERR_ARG, "bad rank %d of %d", rank, nranks);
+  const double t0 = now_ms();
+  DeviceCtx &d0 = g_dev[0];
+  CK(cudaSetDevice(d0.dev));
+  size_t need = (size_t)rt_rank_num_rows(H, rank, nranks) * W * 3 + 64;
+  if ((r = dev_realloc(d0.rank_buf, d0.rank_cap, need)) != RT_OK) return r;
+  RankPlan plan;
+  if ((r = enqueue_rank(d0, W, H, rank, nranks, d0.rank_buf, &plan)) != RT_OK) return r;
+  CK(cudaStreamSynchronize(d0.stream));
+  if (dev_rows_out) *dev_rows_out = d0.rank_buf;
+  if (nbytes) *nbytes = plan.bytes;
+  r = collect_stats(1, W, H, &plan, stats, 0.0, t0);
+  if (stats) { stats->pixels = (uint64_t)plan.rows * W; stats->rays_primary = stats->pixels; }
+  return r;
+}
+
+int rt_assemble_device(int W, int H, int nranks, const void *dev_staging, const int64_t *rank_offsets,
+                       void *dev_frame) {
+  if (!g_ndev) return set_err(RT_ERR_NO_DEVICE, "rt_assemble_device before rt_init");
+  if (W <= 0 || H <= 0 || nranks < 1 || nranks > RT_MAX_GPUS || !dev_staging || !rank_offsets || !dev_frame)
+    return set_err(RT_ERR_ARG, "bad rt_assemble_device argument");
+  DeviceCtx &d0 = g_dev[0];
+  CK(cudaSetDevice(d0.dev));
+  AssembleArgs a;
+  memset(&a, 0, sizeof a);
+  for (int i = 0; i < nranks; i++) a.rank_off[i] = rank_offsets[i];
+  a.width = W; a.height = H; a.nranks = nranks; a.band_h = band_rows();
+  k_assemble<<<d0.sm_count * 8, 256, 0, d0.stream>>>(a, (const uint8_t *)dev_staging, (uint8_t *)dev_frame);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(d0.stream));
+  return RT_OK;
+}
+
+int rt_init_device(int ordinal) {
+  if (g_ndev) rt_shutdown();
+  int avail = 0;
+  cudaError_t e = cudaGetDeviceCount(&avail);
+  if (e != cudaSuccess || avail <= 0)
+    return set_err(RT_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU path",
+                   e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  if (ordinal < 0 || ordinal >= avail) return set_err(RT_ERR_ARG, "device ordinal %d out of range (0..%d)", ordinal, avail - 1);
+  DeviceCtx &d = g_dev[0];
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, ordinal));
+  if (prop.major != 10)
+    return set_err(RT_ERR_NO_DEVICE, "device %d (%s, sm_%d%d) is not a Blackwell sm_100 part", ordinal, prop.name, prop.major, prop.minor);
+  CK(cudaSetDevice(ordinal));
+  d.dev = ordinal;
+  d.sm_count = prop.multiProcessorCount;
+  CK(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
+  CK(cudaMalloc((void **)&d.qcount, 8 * sizeof(int)));
+  CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
+  g_ndev = 1;
+  return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,89 @@
+/*
+ * host/raytrace_main.c -- the reference CLI (C/raycast.c:19-69), same contract:
+ *     raytrace WIDTH HEIGHT INPUT_SCENE OUTPUT_IMAGE
+ * wrong argc -> usage on stdout, exit(0); unopenable files -> "Error: ..." on stderr,
+ * exit(1); on success one stdout line
+ *     Time (sec) to create a WxH image with N shape(s) and M light(s): T
+ * timing render + P3 write like the reference does.  Differences, all deliberate:
+ * the scene is opened "r" (the reference's "r+" needs a writable file), json_data_t is
+ * zeroed (the reference leaves num_lights uninitialised),
+ * sizes are size_t, and the counts are read before the struct is freed.
+ * RT_VERBOSE=1 adds a second line with the GPU-side statistics.
+ */
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <sys/time.h>
+#include "raycast_host.h"
+
+static double now_sec(void) {
+  struct timeval tv;
+  gettimeofday(&tv, NULL);
+  return (double)tv.tv_sec + (double)tv.tv_usec / 1e6;
+}
+
+int main(int argc, char **argv) {
+  if (argc != 5) {
+    printf("Usage: raytrace WIDTH HEIGHT INPUT_SCENE OUTPUT_IMAGE\n");
+    exit(0);
+  }
+  int width = atoi(argv[1]);
+  int height = atoi(argv[2]);
+
+  FILE *input_json = fopen(argv[3], "r");
+  if (input_json == NULL) {
+    fprintf(stderr, "Error: Unable to open the input scene file: %s\n", argv[3]);
+    exit(1);
+  }
+  FILE *output_image = fopen(argv[4], "wb");
+  if (output_image == NULL) {
+    fprintf(stderr, "Error: Unable to open the output image file: %s\n", argv[4]);
+    exit(1);
+  }
+  if (width <= 0 || height <= 0) {
+    fprintf(stderr, "Error: WIDTH and HEIGHT must be positive integers.\n");
+    exit(1);
+  }
+
+  json_data_t *json_struct = (json_data_t *)calloc(1, sizeof(json_data_t));
+  parse_json(input_json, json_struct);
+  fclose(input_json);
+  const int num_shapes = json_struct->num_shapes, num_lights = json_struct->num_lights;
+
+  PPMFormat photo_data;
+  photo_data.maxColor = 255;
+  photo_data.depth = 3;
+  photo_data.tupleType = NULL;
+  photo_data.height = height;
+  photo_data.width = width;
+  const size_t bytes = (size_t)width * (size_t)height * 3u;
+  photo_data.size = bytes > (size_t)INT32_MAX ? INT32_MAX : (int)bytes;
+  photo_data.pixmap = (uint8_t *)malloc(bytes);
+  if (photo_data.pixmap == NULL) {
+    fprintf(stderr, "Error: Unable to allocate a %dx%d image.\n", width, height);
+    exit(1);
+  }
+
+  double start = now_sec();
+  raycast(json_struct, photo_data);
+  double rendered = now_sec();
+  if (getenv("RT_PPM_P6")) ppm_WriteOutP6(photo_data, output_image);
+  else ppm_WriteOutP3(photo_data, output_image);
+  fclose(output_image);
+  free(photo_data.pixmap);
+  free(json_struct);
+  double end = now_sec();
+
+  printf("Time (sec) to create a %dx%d image with %d shape(s) and %d light(s): %f\n", width, height,
+         num_shapes, num_lights, end - start);
+  if (getenv("RT_VERBOSE")) {
+    const rt_stats *st = rt_host_last_stats();
+    double rays = (double)(st->rays_primary + st->rays_reflection + st->rays_shadow);
+    printf("B200: render %.6f s (kernels %.3f ms, gather %.3f ms), write %.6f s, %.0f rays, "
+           "%.1f Mrays/s, %d GPU(s)\n",
+           rendered - start, st->ms_kernels, st->ms_gather, end - rendered, rays,
+           rays / 1e3 / (st->ms_kernels > 0 ? st->ms_kernels : 1), rt_device_count());
+  }
+  rt_shutdown();
+  return 0;
+}

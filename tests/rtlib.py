@@ -1,0 +1,125 @@
+"""Test-side helpers: ctypes bindings of the oracle (oracle/liboracle.so), of the patched
+reference (oracle/_ref/libref.so, optional) and of the product package."""
+import ctypes as C
+import importlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+pkg = importlib.import_module("raytracing-programs_b200")
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+SCENES = os.path.join(GOLDEN, "scenes")
+REF_ROOT = "/root/reference"
+
+
+class OrcCounters(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("rays_primary", "rays_reflection", "rays_shadow", "hit_points",
+                                           "tests_sphere", "tests_plane", "tests_quadric", "shadow_occluded")]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+_oracle = None
+_ref = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        path = os.path.join(ROOT, "oracle", "liboracle.so")
+        if not os.path.exists(path):
+            raise RuntimeError("oracle/liboracle.so missing: run `make -C oracle` (or __graft_entry__.build())")
+        o = C.CDLL(path)
+        o.orc_render_rows.argtypes = [C.POINTER(pkg.RtScene), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                      C.POINTER(OrcCounters)]
+        o.orc_render_row_list.argtypes = [C.POINTER(pkg.RtScene), C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int,
+                                          C.c_void_p, C.c_int, C.POINTER(OrcCounters)]
+        fp = C.POINTER(C.c_float)
+        o.orc_isect_sphere.argtypes = [fp, fp, fp, C.c_float, fp]
+        o.orc_isect_plane.argtypes = [fp, fp, fp, fp, fp]
+        o.orc_isect_quadric.argtypes = [fp, fp, fp, fp]
+        _oracle = o
+    return _oracle
+
+
+def ref_available():
+    return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libref.so"))
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        r = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libref.so"))
+        r.ref_scene_load.restype = C.c_void_p
+        r.ref_scene_load.argtypes = [C.c_char_p]
+        r.ref_scene_free.argtypes = [C.c_void_p]
+        for f in ("ref_scene_num_shapes", "ref_scene_num_lights"):
+            getattr(r, f).argtypes = [C.c_void_p]
+        for f in ("ref_scene_cam_w", "ref_scene_cam_h"):
+            getattr(r, f).argtypes = [C.c_void_p]
+            getattr(r, f).restype = C.c_float
+        r.ref_scene_dump_shapes.argtypes = [C.c_void_p, C.c_void_p]
+        r.ref_scene_dump_lights.argtypes = [C.c_void_p, C.c_void_p]
+        r.ref_render_rows.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        r.ref_render_row_list.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_int]
+        fp = C.POINTER(C.c_float)
+        r.ref_isect_sphere.argtypes = [fp, fp, fp, C.c_float, fp]
+        r.ref_isect_plane.argtypes = [fp, fp, fp, fp, fp]
+        r.ref_isect_quadric.argtypes = [fp, fp, fp, fp]
+        _ref = r
+    return _ref
+
+
+def ncores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def oracle_render(scene, W, H, rows=None, threads=None, counters=False):
+    """Oracle image (all rows, or the given list of rows) as uint8 [n, W, 3]."""
+    if isinstance(scene, (str, os.PathLike)):
+        scene = pkg.load_scene(scene)
+    rows = list(range(H)) if rows is None else list(rows)
+    out = np.zeros((len(rows), W, 3), dtype=np.uint8)
+    arr = (C.c_int * len(rows))(*rows)
+    ct = OrcCounters()
+    oracle().orc_render_row_list(C.byref(scene), W, H, arr, len(rows), out.ctypes.data_as(C.c_void_p),
+                                 threads or ncores(), C.byref(ct))
+    return (out, ct) if counters else out
+
+
+def ref_render(scene_path, W, H, rows=None, threads=None):
+    r = ref()
+    h = r.ref_scene_load(os.fsencode(scene_path))
+    if not h:
+        raise RuntimeError(f"reference cannot open {scene_path}")
+    rows = list(range(H)) if rows is None else list(rows)
+    out = np.zeros((len(rows), W, 3), dtype=np.uint8)
+    arr = (C.c_int * len(rows))(*rows)
+    r.ref_render_row_list(h, W, H, arr, len(rows), out.ctypes.data_as(C.c_void_p), threads or ncores())
+    r.ref_scene_free(h)
+    return out
+
+
+def compare(a, b):
+    """Parity report between two uint8 [.., W, 3] images."""
+    a = np.asarray(a).reshape(-1, 3).astype(np.int16)
+    b = np.asarray(b).reshape(-1, 3).astype(np.int16)
+    diff = np.abs(a - b).max(axis=1)
+    n = diff.size
+    bad = int((diff > 0).sum())
+    return {"pixels": n, "identical": n - bad, "identical_frac": (n - bad) / max(n, 1),
+            "max_abs_diff": int(diff.max()) if n else 0, "gt1": int((diff > 1).sum()),
+            "divergent_idx": np.nonzero(diff > 0)[0][:64].tolist()}
+
+
+def fvec(*v):
+    return (C.c_float * len(v))(*v)
