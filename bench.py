@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 render loop (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                  [--workload c4|c5|c2|c3|c1] [--size PX]
+
+A "step" renders one full frame of the workload.  Default workload (N = 1..8): BASELINE
+config 4, the synthetic 1024-sphere + 8-plane + 16-light scene at 16384 x 16384, depth 7.
+Rank 0 prints ONE JSON line:
+  value     Mrays/s (primary + reflection + shadow rays of the reference semantics), scene
+            resident on the GPU(s), frame left in GPU 0 memory; device time (CUDA events on
+            the launching streams, max over ranks).
+  e2e       same metric through the public call a user makes (scene flatten + H2D upload,
+            render, band gather, D2H into pinned host memory), host clock around the call.
+  roofline  k_shade<LB> (the intersection/shading kernel) against the FP32 peak.
+  cpu_baseline  the patched reference C path (oracle/_ref/libref.so) on the host cores, on
+            sampled full-width rows of the same frame; the same rows double as the
+            full-size parity check ("parity").
+N > 1 is launched by torchrun (one process per GPU); the image is split into interleaved
+row bands, each rank renders its bands, rank 0 gathers them over NCCL and de-interleaves.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+pkg = importlib.import_module("raytracing-programs_b200")
+
+GOLD = os.path.join(ROOT, "tests", "golden", "scenes")
+WORKLOADS = {
+    "c1": ("C1: examples/simple.scene 1000x1000 (4 shapes, 1 light)", os.path.join(GOLD, "ref_simple.scene"), 1000, 1000),
+    "c2": ("C2: examples/reflection.scene 3840x2160 (15 shapes, 1 light, depth 7)", os.path.join(GOLD, "ref_reflection.scene"), 3840, 2160),
+    "c3": ("C3: examples/quadric.scene 7680x4320 (3 quadrics + sphere + plane, 2 lights)", os.path.join(GOLD, "ref_quadric.scene"), 7680, 4320),
+    "c4": ("C4: synthetic 1024 spheres + 8 planes, 16 lights, 16384x16384, depth 7 (scenes/c4_syn1032.scene, seed 1234)",
+           os.path.join(ROOT, "scenes", "c4_syn1032.scene"), 16384, 16384),
+    "c5": ("C5: synthetic 2040 spheres + 16 planes + 2040 quadrics, 16 lights, 32768x32768, depth 7 (scenes/c5_syn4096.scene, seed 4321)",
+           os.path.join(ROOT, "scenes", "c5_syn4096.scene"), 32768, 32768),
+}
+FP32_LANES = 148 * 128
+
+
+def peaks():
+    p = {"sm_max_mhz": 1965.0, "hbm_gbs": 6650.0, "src": "fallback"}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            m = json.load(f)
+        p.update(sm_max_mhz=float(m.get("sm_max_mhz", 1965.0)), hbm_gbs=float(m.get("hbm_gbs", 6650.0)), src="measured")
+    except Exception:
+        pass
+    p["fp32_tflops"] = FP32_LANES * 2 * p["sm_max_mhz"] * 1e6 / 1e12
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, pw, reasons = [], [], [], set()
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = [s for s, p in zip(sm, pw) if p > 250] or sm
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def scene_bytes(sc):
+    return sc.num_shapes * C.sizeof(pkg.RtShape) + sc.num_lights * C.sizeof(pkg.RtLight) + 16
+
+
+def sample_rows(H, n):
+    n = max(1, min(n, H))
+    return sorted({int((i + 0.5) * H / n) for i in range(n)})
+
+
+def run_reference_arm(args, name, scene_path, W, H):
+    """--impl reference: the reference's own CPU path on all host threads, bounded sample per step."""
+    import rtlib
+    cores = rtlib.ncores()
+    kind = "reference" if rtlib.ref_available() else "port"
+    rows = sample_rows(H, max(cores, 8) if W * 31 > 200000 else min(H, 64 * cores))
+    sc = pkg.load_scene(scene_path)
+    _, ct = rtlib.oracle_render(sc, W, H, rows=rows, counters=True)          # ray count of the sample (untimed)
+    rays = ct.rays_primary + ct.rays_reflection + ct.rays_shadow
+
+    def step():
+        if kind == "reference":
+            rtlib.ref_render(scene_path, W, H, rows=rows, threads=cores)
+        else:
+            rtlib.oracle_render(sc, W, H, rows=rows, threads=cores)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    v = rays / dt / 1e6
+    sample = f"{len(rows)} full-width rows of the {W}x{H} frame per step ({rays} rays), {cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": "Mrays/s (primary+secondary)", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 roots)", "data": "synthetic",
+        "config": {"workload": name, "width": W, "height": H, "shapes": sc.num_shapes, "lights": sc.num_lights},
+        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--size", type=int, default=0, help="override the frame to SIZE x SIZE (debug)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the C1-C3 side measurements")
+    args = ap.parse_args()
+
+    name, scene_path, W, H = WORKLOADS[args.workload]
+    if args.size:
+        W = H = args.size
+        name += f" [frame overridden to {W}x{H}]"
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank == 0:
+            run_reference_arm(args, name, scene_path, W, H)
+        return
+
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    r = pkg.Renderer(device=local_rank)          # raises RtError without a B200: no CPU path
+    sc = pkg.load_scene(scene_path)
+    r.upload(sc)
+    pk = peaks()
+
+    my_rows = len(pkg.rank_rows(H, rank, world))
+    my_bytes = my_rows * W * 3
+    sizes = [len(pkg.rank_rows(H, k, world)) * W * 3 for k in range(world)]
+    offs = [0]
+    for s in sizes[:-1]:
+        offs.append(offs[-1] + ((s + 255) // 256) * 256)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+    rank_buf = torch.empty(my_bytes + 256, dtype=torch.uint8, device=dev)
+    staging = frame = host_frame = None
+    if rank == 0:
+        frame = torch.empty(W * H * 3, dtype=torch.uint8, device=dev)
+        host_frame = torch.empty(W * H * 3, dtype=torch.uint8, pin_memory=True)
+        if world > 1:
+            staging = torch.empty(offs[-1] + sizes[-1] + 256, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def gather_to_rank0():
+        """Band gather: every rank's rows to rank 0 over NCCL (NVLink), then de-interleave."""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        if rank == 0:
+            staging[:sizes[0]].copy_(rank_buf[:sizes[0]])
+            reqs = [dist.P2POp(dist.irecv, staging[offs[k]:offs[k] + sizes[k]], k) for k in range(1, world)]
+        else:
+            reqs = [dist.P2POp(dist.isend, rank_buf[:my_bytes], 0)]
+        for w in dist.batch_isend_irecv(reqs):
+            w.wait()
+        if rank == 0:
+            r.assemble(W, H, world, staging.data_ptr(), offs, frame.data_ptr())
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
+    def step_resident():
+        """One frame, scene resident; returns (device ms, stats)."""
+        if world == 1:
+            _, _, st = r.raycast_rank(W, H, 0, 1, frame.data_ptr())
+            return st.ms_kernels, st
+        _, _, st = r.raycast_rank(W, H, rank, world, rank_buf.data_ptr())
+        return st.ms_kernels + gather_to_rank0(), st
+
+    def step_e2e():
+        """The public call: flatten + upload the scene, render, gather, D2H to pinned memory."""
+        r.upload(sc)
+        if world == 1:
+            return r.raycast_into(W, H, host_frame.data_ptr())
+        _, _, st = r.raycast_rank(W, H, rank, world, rank_buf.data_ptr())
+        gather_to_rank0()
+        if rank == 0:
+            host_frame.copy_(frame, non_blocking=True)
+            torch.cuda.synchronize()
+        return st
+
+    # ---- value: device-timed, inputs resident -----------------------------------------
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    t_wall0 = time.perf_counter()
+    dev_ms, agg = 0.0, None
+    for _ in range(args.steps):
+        flush.fill_(1)                               # L2 flush between timed iterations
+        torch.cuda.synchronize()
+        ms, st = step_resident()
+        dev_ms += ms
+        agg = st
+    barrier()
+    wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    clocks = sampler.stop() if sampler else None
+
+    def allsum(vals):
+        t = torch.tensor(vals, dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t.tolist()
+
+    def allmax(v):
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    rays_p, rays_r, rays_s, hitp, flops, launches = allsum([agg.rays_primary, agg.rays_reflection, agg.rays_shadow,
+                                                             agg.hit_points, agg.flops, agg.kernel_launches])
+    rays = rays_p + rays_r + rays_s
+    ms_step = allmax(dev_ms / args.steps)
+    wall_step = allmax(wall_ms / args.steps)
+    value = rays / ms_step / 1e3
+
+    # ---- e2e ---------------------------------------------------------------------------
+    step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    e2e_ms = allmax((time.perf_counter() - t0) * 1e3 / args.steps)
+    e2e = {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "ms_per_step": e2e_ms,
+           "h2d_bytes_per_step": scene_bytes(sc) * world, "d2h_bytes_per_step": W * H * 3}
+
+    if rank != 0:
+        r.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (k_shade) on rank 0 -----------------------------
+    shade_ms = agg.ms_shade / max(agg.launches_shade, 1)
+    ach = agg.flops_shade / max(agg.ms_shade, 1e-9) / 1e9            # TFLOP/s
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "k_shade_traffic.json")) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    roof = {"bound": "fp32", "kernel": "k_shade", "achieved": ach, "peak": pk["fp32_tflops"], "unit": "TFLOP/s",
+            "frac": ach / pk["fp32_tflops"], "traffic": traffic, "peak_src": f"148 SM x 128 lanes x 2 x {pk['sm_max_mhz']:.0f} MHz ({pk['src']} clock)",
+            "launches": int(agg.launches_shade), "avg_launch_ms": shade_ms, "kernel_share_of_step": agg.ms_shade / max(agg.ms_kernels, 1e-9),
+            "flops_per_launch": agg.flops_shade / max(agg.launches_shade, 1),
+            "framebuffer_write_gbs": (W * H * 3 / world) / max(agg.ms_finalize, 1e-9) / 1e6, "hbm_peak_gbs": pk["hbm_gbs"]}
+    if clocks and clocks.get("sm_mhz"):
+        roof["frac_at_sampled_clock"] = ach / (FP32_LANES * 2 * clocks["sm_mhz"] * 1e6 / 1e12)
+
+    out = {"metric": "Mrays/s (primary+secondary)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms_step, "wall_ms_per_step": wall_step, "higher_is_better": True,
+           "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 roots)", "data": "synthetic",
+           "config": {"workload": name, "width": W, "height": H, "shapes": sc.num_shapes, "lights": sc.num_lights,
+                      "parallelism": f"row bands of {pkg.load_library().rt_band_height()} rows interleaved over {world} GPU(s)",
+                      "l2": "256 MB flush between timed steps; per-tile working set > L2",
+                      "rays_per_pixel": rays / (W * H), "rays": {"primary": rays_p, "reflection": rays_r, "shadow": rays_s}},
+           "mpixels_per_s": W * H / ms_step / 1e3, "tflops_fp32_algorithmic": flops / ms_step / 1e9,
+           "frac_fp32_peak": flops / ms_step / 1e9 / (pk["fp32_tflops"] * world),
+           "roofline": roof, "e2e": e2e, "gpu_launches": int(launches * args.steps + (args.steps if world > 1 else 0)),
+           "clocks": clocks}
+
+    # ---- cpu_baseline + full-size parity on sampled rows ---------------------------------
+    if not args.no_cpu:
+        import rtlib
+        cores = rtlib.ncores()
+        kind = "reference" if rtlib.ref_available() else "port"
+        per_row_rays = rays / H
+        budget_rows = max(1, int(0.9e6 * cores / max(per_row_rays, 1)))      # ~15 s at ~0.06 Mrays/s/core
+        rows = sample_rows(H, min(H, max(budget_rows, min(cores, H)) if per_row_rays > 1e4 else min(H, 256)))
+        t0 = time.perf_counter()
+        cpu_img = rtlib.ref_render(scene_path, W, H, rows=rows, threads=cores) if kind == "reference" \
+            else rtlib.oracle_render(sc, W, H, rows=rows, threads=cores)
+        cpu_s = time.perf_counter() - t0
+        gpu_img = host_frame.numpy().reshape(H, W, 3)[rows]
+        rep = rtlib.compare(gpu_img, cpu_img)
+        sample_rays = rays * len(rows) / H
+        out["cpu_baseline"] = {"value": sample_rays / cpu_s / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind,
+                               "sample": f"{len(rows)} full-width rows of the {W}x{H} frame (~{sample_rays:.0f} rays, "
+                                         f"frame-average rays/row), {cpu_s:.1f} s on {cores} threads"}
+        out["parity"] = {"against": "patched reference C path" if kind == "reference" else "oracle port", "rows": len(rows),
+                         "pixels": rep["pixels"], "identical_frac": rep["identical_frac"], "max_abs_diff": rep["max_abs_diff"],
+                         "divergent_pixels": rep["pixels"] - rep["identical"]}
+
+    # ---- the small shipped configs, for the record (N = 1 only) --------------------------
+    if world == 1 and not args.no_extra and not args.size:
+        extra = {}
+        for key in ("c1", "c2", "c3"):
+            nm, sp, w, h = WORKLOADS[key]
+            r.upload(sp)
+            for _ in range(3):
+                p, st = r.raycast_device(w, h)
+            ms = []
+            for _ in range(5):
+                p, st = r.raycast_device(w, h)
+                ms.append(st.ms_kernels)
+            m = statistics.median(ms)
+            extra[key] = {"workload": nm, "ms_kernels": m, "mrays_per_s": st.rays / m / 1e3, "mpixels_per_s": w * h / m / 1e3,
+                          "rays": int(st.rays), "launches": int(st.kernel_launches)}
+        out["other_configs"] = extra
+    print(json.dumps(out))
+    r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

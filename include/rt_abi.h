@@ -94,7 +94,12 @@ typedef struct rt_stats {
   uint64_t quadric_tests_o, quadric_tests_d;
   uint64_t kernel_launches;
   double flops;                 /* algorithmic flops executed, SURVEY.md section 8a convention */
+  double flops_shade;           /* the part of flops executed by the k_shade launches */
   double ms_kernels;            /* device time of the render kernels (max over GPUs) */
+  double ms_primary;            /* per kernel class, CUDA events around every launch on the */
+  double ms_shade;              /* launching stream, summed over launches (GPU 0 / this rank) */
+  double ms_finalize;
+  uint64_t launches_shade;
   double ms_gather;             /* band gather to GPU 0 */
   double ms_total;              /* the whole call, host clock */
 } rt_stats;
@@ -125,10 +130,11 @@ int rt_render(int width, int height, uint8_t *rgb_out, rt_stats *stats);
 int rt_render_device(int width, int height, void **dev_rgb_out, rt_stats *stats);
 
 /* One-process-per-GPU mode (torchrun ranks): render only the bands of `rank` out of
- * `nranks` on the current device 0 of this process into a library-owned device buffer
- * holding this rank's rows back to back (band order). The caller gathers the rank
+ * `nranks` on this process's device into dev_dst (caller-owned device memory of at least
+ * 3*W*rt_rank_num_rows() bytes) or, when dev_dst is NULL, into a library-owned buffer;
+ * the rank's rows lie back to back (band order). The caller gathers the rank
  * buffers with its own collective and de-interleaves with rt_band_rows(). */
-int rt_render_rank(int width, int height, int rank, int nranks,
+int rt_render_rank(int width, int height, int rank, int nranks, void *dev_dst,
                    void **dev_rows_out, size_t *nbytes, rt_stats *stats);
 
 /* De-interleave gathered rank buffers (rank r's rows start at dev_staging +

@@ -40,8 +40,9 @@ class RtStats(C.Structure):
         "pixels", "rays_primary", "rays_reflection", "rays_shadow", "hit_points",
         "sphere_tests_o", "sphere_tests_d", "plane_tests_o", "plane_tests_d",
         "quadric_tests_o", "quadric_tests_d", "kernel_launches")] + [
-        ("flops", C.c_double), ("ms_kernels", C.c_double), ("ms_gather", C.c_double),
-        ("ms_total", C.c_double)]
+        ("flops", C.c_double), ("flops_shade", C.c_double), ("ms_kernels", C.c_double),
+        ("ms_primary", C.c_double), ("ms_shade", C.c_double), ("ms_finalize", C.c_double),
+        ("launches_shade", C.c_uint64), ("ms_gather", C.c_double), ("ms_total", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -73,7 +74,7 @@ def load_library():
     lib.rt_scene_upload.argtypes = [C.POINTER(RtScene)]
     lib.rt_render.argtypes = [C.c_int, C.c_int, C.c_void_p, C.POINTER(RtStats)]
     lib.rt_render_device.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(RtStats)]
-    lib.rt_render_rank.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p),
+    lib.rt_render_rank.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_size_t), C.POINTER(RtStats)]
     lib.rt_assemble_device.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p,
                                        C.POINTER(C.c_int64), C.c_void_p]
@@ -153,11 +154,12 @@ class Renderer:
         _check(self.lib, self.lib.rt_render_device(width, height, C.byref(p), C.byref(st)), "rt_render_device")
         return p.value, st
 
-    def raycast_rank(self, width, height, rank, nranks):
+    def raycast_rank(self, width, height, rank, nranks, dst_ptr=None):
         st = RtStats()
         p = C.c_void_p()
         n = C.c_size_t()
-        _check(self.lib, self.lib.rt_render_rank(width, height, rank, nranks, C.byref(p), C.byref(n), C.byref(st)),
+        _check(self.lib, self.lib.rt_render_rank(width, height, rank, nranks, C.c_void_p(dst_ptr), C.byref(p),
+                                                 C.byref(n), C.byref(st)),
                "rt_render_rank")
         return p.value, n.value, st
 

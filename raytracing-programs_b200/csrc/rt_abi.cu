@@ -61,6 +61,9 @@ struct DeviceCtx {
   uint8_t *staging = nullptr; size_t staging_cap = 0;   // device 0 only
   uint8_t *frame = nullptr; size_t frame_cap = 0;       // device 0 only
   int grid_primary = 0, grid_shade = 0, grid_fin = 0;
+  // one event before every launch (+1 at the end): per-kernel-class device times
+  std::vector<cudaEvent_t> evpool;
+  std::vector<char> evkind;   // 'p' primary, 's' shade, 'f' finalize
 };
 
 DeviceCtx g_dev[RT_MAX_GPUS];
@@ -139,6 +142,7 @@ void free_device(DeviceCtx &d) {
   if (d.ev1) cudaEventDestroy(d.ev1);
   if (d.ev2) cudaEventDestroy(d.ev2);
   if (d.stream) cudaStreamDestroy(d.stream);
+  for (cudaEvent_t e : d.evpool) cudaEventDestroy(e);
   d = DeviceCtx();
 }
 
@@ -331,6 +335,18 @@ int pick_lb(int n_lights) {
 
 struct RankPlan { int64_t rows; size_t bytes; int launches; };
 
+int mark(DeviceCtx &d, char kind) {
+  size_t i = d.evkind.size();
+  if (i >= d.evpool.size()) {
+    cudaEvent_t e;
+    CK(cudaEventCreate(&e));
+    d.evpool.push_back(e);
+  }
+  d.evkind.push_back(kind);
+  CK(cudaEventRecord(d.evpool[i], d.stream));
+  return RT_OK;
+}
+
 // Enqueue the whole render of `rank`'s rows on device d (asynchronous).
 int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst, RankPlan *plan) {
   CK(cudaSetDevice(d.dev));
@@ -368,6 +384,8 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     q[k].count = nullptr;
   }
   CK(cudaMemsetAsync(d.counters, 0, CT_COUNT * sizeof(unsigned long long), d.stream));
+  d.evkind.clear();
+  int mr;
   CK(cudaEventRecord(d.ev0, d.stream));
   for (long long first = 0; first < px_total; first += (long long)tile) {
     TileGeom tg;
@@ -377,11 +395,13 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     CK(cudaMemsetAsync(d.qcount, 0, 8 * sizeof(int), d.stream));
     HitQueue q0 = q[0]; q0.count = d.qcount;
     int gp = (tg.n_px + 255) / 256; if (gp > d.grid_primary) gp = d.grid_primary;
+    if ((mr = mark(d, 'p')) != RT_OK) return mr;
     k_primary<<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, d.counters);
     plan->launches++;
     for (int level = 0; level < 7; level++) {
       HitQueue qin = q[level & 1], qout = q[(level + 1) & 1];
       qin.count = d.qcount + level; qout.count = d.qcount + level + 1;
+      if ((mr = mark(d, 's')) != RT_OK) return mr;
       switch (lb) {
         case 1: launch_shade<1>(d, d.grid_shade, level, qin, qout); break;
         case 2: launch_shade<2>(d, d.grid_shade, level, qin, qout); break;
@@ -392,10 +412,12 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
       plan->launches++;
     }
     int gf = (tg.n_px / 4 + 256) / 256; if (gf > d.grid_fin) gf = d.grid_fin;
+    if ((mr = mark(d, 'f')) != RT_OK) return mr;
     k_finalize<<<gf, 256, 0, d.stream>>>(tg, d.acc, d.c0, dst);
     plan->launches++;
     CK(cudaGetLastError());
   }
+  if ((mr = mark(d, 'e')) != RT_OK) return mr;
   CK(cudaEventRecord(d.ev1, d.stream));
   return RT_OK;
 }
@@ -421,12 +443,26 @@ int collect_stats(int ndev, int W, int H, const RankPlan *plans, rt_stats *st, d
     s.quadric_tests_o += c[CT_QUAD_O]; s.quadric_tests_d += c[CT_QUAD_D];
     s.kernel_launches += plans[i].launches;
     // SURVEY.md section 8a flop convention
-    s.flops += 10.0 * c[CT_SPH_O] + 8.0 * c[CT_SPH_D] + 8.0 * c[CT_PLN_O] + 6.0 * c[CT_PLN_D] +
+    const double all = 10.0 * c[CT_SPH_O] + 8.0 * c[CT_SPH_D] + 8.0 * c[CT_PLN_O] + 6.0 * c[CT_PLN_D] +
                21.0 * c[CT_QUAD_O] + 37.0 * c[CT_QUAD_D] + 3.0 * c[CT_CANDIDATES] +
                77.0 * c[CT_LIGHT_SAMPLES] + 12.0 * c[CT_RAYS_SHADOW] + 21.0 * c[CT_RAYS_REFLECTION] +
                20.0 * c[CT_HIT_POINTS];
+    // k_primary's share: per pixel every sphere (direction part only), plane and quadric once
+    const double px = (double)plans[i].rows * W;
+    const double prim = px * (17.0 + 8.0 * d.sc.n_spheres + 14.0 * d.sc.n_planes + 58.0 * d.sc.n_quadrics) +
+                        20.0 * c[CT_PRIMARY_HITS];
+    s.flops += all + px * 17.0 + 20.0 * c[CT_PRIMARY_HITS];
+    s.flops_shade += all + px * 17.0 + 20.0 * c[CT_PRIMARY_HITS] - prim;
+    if (i == 0) {
+      for (size_t k = 0; k + 1 < d.evkind.size(); k++) {
+        float t = 0;
+        CK(cudaEventElapsedTime(&t, d.evpool[k], d.evpool[k + 1]));
+        if (d.evkind[k] == 'p') s.ms_primary += t;
+        else if (d.evkind[k] == 's') { s.ms_shade += t; s.launches_shade++; }
+        else if (d.evkind[k] == 'f') s.ms_finalize += t;
+      }
+    }
   }
-  s.flops += 17.0 * (double)s.pixels;
   s.ms_kernels = ms_k;
   s.ms_gather = ms_gather;
   s.ms_total = now_ms() - t0;
@@ -523,19 +559,24 @@ int rt_render(int W, int H, uint8_t *rgb_out, rt_stats *stats) {
   return RT_OK;
 }
 
-int rt_render_rank(int W, int H, int rank, int nranks, void **dev_rows_out, size_t *nbytes, rt_stats *stats) {
+int rt_render_rank(int W, int H, int rank, int nranks, void *dev_dst, void **dev_rows_out, size_t *nbytes,
+                   rt_stats *stats) {
   int r = check_render_args(W, H);
   if (r != RT_OK) return r;
   if (nranks < 1 || rank < 0 || rank >= nranks) return set_err(RT_ERR_ARG, "bad rank %d of %d", rank, nranks);
   const double t0 = now_ms();
   DeviceCtx &d0 = g_dev[0];
   CK(cudaSetDevice(d0.dev));
-  size_t need = (size_t)rt_rank_num_rows(H, rank, nranks) * W * 3 + 64;
-  if ((r = dev_realloc(d0.rank_buf, d0.rank_cap, need)) != RT_OK) return r;
+  uint8_t *dst = (uint8_t *)dev_dst;
+  if (!dst) {
+    size_t need = (size_t)rt_rank_num_rows(H, rank, nranks) * W * 3 + 64;
+    if ((r = dev_realloc(d0.rank_buf, d0.rank_cap, need)) != RT_OK) return r;
+    dst = d0.rank_buf;
+  }
   RankPlan plan;
-  if ((r = enqueue_rank(d0, W, H, rank, nranks, d0.rank_buf, &plan)) != RT_OK) return r;
+  if ((r = enqueue_rank(d0, W, H, rank, nranks, dst, &plan)) != RT_OK) return r;
   CK(cudaStreamSynchronize(d0.stream));
-  if (dev_rows_out) *dev_rows_out = d0.rank_buf;
+  if (dev_rows_out) *dev_rows_out = dst;
   if (nbytes) *nbytes = plan.bytes;
   r = collect_stats(1, W, H, &plan, stats, 0.0, t0);
   if (stats) { stats->pixels = (uint64_t)plan.rows * W; stats->rays_primary = stats->pixels; }

@@ -10,7 +10,7 @@
 #include "ppm_out.h"
 
 void ppm_WriteOutP3(PPMFormat inData, FILE *outFile) {
-  char lut[256][4];
+  char lut[256][8];   /* "255\n" + NUL needs 5 */
   uint8_t lut_len[256];
   for (int v = 0; v < 256; v++) lut_len[v] = (uint8_t)sprintf(lut[v], "%d\n", v);
 
