@@ -65,7 +65,7 @@ def load_library():
     global _lib
     if _lib is not None:
         return _lib
-    path = os.path.join(LIB_DIR, "librt_b200.so")
+    path = os.environ.get("RT_B200_LIB") or os.path.join(LIB_DIR, "librt_b200.so")   # env: tuning variants only
     if not os.path.exists(path):
         raise RtError(f"{path} is missing: run `python __graft_entry__.py` (build) first; "
                       "there is no fallback renderer")

@@ -227,7 +227,7 @@ int rt_scene_upload(const rt_scene *scene) {
       (scene->num_shapes > 0 && !scene->shapes) || (scene->num_lights > 0 && !scene->lights))
     return set_err(RT_ERR_ARG, "bad scene argument");
   const int n = scene->num_shapes, nl = scene->num_lights;
-  std::vector<float4> sph, sph_prim, pln, quad, mat(2 * (size_t)n + 1), lights(4 * (size_t)nl + 1);
+  std::vector<float4> sph, sph_hot, sph_prim, pln, quad, mat(2 * (size_t)n + 1), lights(4 * (size_t)nl + 1);
   std::vector<int> sph_idx, pln_idx, quad_idx;
   std::vector<int2> slot((size_t)n + 1);
   for (int i = 0; i < n; i++) {
@@ -240,12 +240,19 @@ int rt_scene_upload(const rt_scene *scene) {
       slot[i] = make_int2(0, (int)sph.size());
       const float r = s.params[0];
       sph.push_back(make_float4(s.position[0], s.position[1], s.position[2], r));
+      { volatile float rr = r * r; sph_hot.push_back(make_float4(s.position[0], s.position[1], s.position[2], rr)); }
       // primary rays start at exactly (0,0,0): temp = o - centre and c of C/raycast.c:581,585
       volatile float t0 = 0.0f - s.position[0], t1 = 0.0f - s.position[1], t2 = 0.0f - s.position[2];
       volatile float p0 = t0 * t0, p1 = t1 * t1, p2 = t2 * t2;
       volatile float s01 = p0 + p1;
       volatile float tt = s01 + p2;
-      sph_prim.push_back(make_float4(t0, t1, t2, fmaf(-r, r, tt)));
+      // reject-filter constant k = 2^-18 (T' + r^2) - (T' - r^2), same formula as k_shade's
+      (void)tt;
+      volatile float rr2 = r * r;
+      volatile float q0 = t0 * t0;
+      volatile float Tp = fmaf(t2, t2, fmaf(t1, t1, q0));
+      volatile float su = Tp + rr2, di = rr2 - Tp;
+      sph_prim.push_back(make_float4(t0, t1, t2, fmaf(RT_FILTER_EPS, su, di)));
       sph_idx.push_back(i);
     } else if (s.type == RT_PLANE) {
       slot[i] = make_int2(1, (int)pln_idx.size());
@@ -262,6 +269,7 @@ int rt_scene_upload(const rt_scene *scene) {
       return set_err(RT_ERR_ARG, "shape %d has unknown type %d", i, s.type);
     }
   }
+  const size_t slot_count_spheres = sph_idx.size();
   for (int l = 0; l < nl; l++) {
     const rt_light &t = scene->lights[l];
     if (t.type != RT_POINT && t.type != RT_SPOTLIGHT) return set_err(RT_ERR_ARG, "light %d has unknown type %d", l, t.type);
@@ -271,14 +279,24 @@ int rt_scene_upload(const rt_scene *scene) {
     lights[4 * l + 2] = make_float4(t.radial[0], t.radial[1], t.radial[2], t.a0);
     lights[4 * l + 3] = make_float4(t.direction[0], t.direction[1], t.direction[2], 0.f);
   }
+  // pad the per-sphere arrays to a multiple of 4 with entries the reject filter never passes
+  // (r*r = -inf => k = -inf) so the hot loops can run unrolled without a tail
+  while (sph_hot.size() % 4) {
+    sph_hot.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));
+    sph.push_back(make_float4(0.f, 0.f, 0.f, 0.f));
+    sph_prim.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));
+    sph_idx.push_back(-2);
+  }
+  const int n_sph_real = (int)slot_count_spheres;
   // one blob, 256-byte aligned sections
   struct Sec { const void *src; size_t bytes; size_t off; };
-  Sec secs[10] = {
+  Sec secs[11] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
       {quad_idx.data(), quad_idx.size() * 4, 0}, {mat.data(), mat.size() * 16, 0},
-      {slot.data(), slot.size() * 8, 0},       {lights.data(), lights.size() * 16, 0}};
+      {slot.data(), slot.size() * 8, 0},       {lights.data(), lights.size() * 16, 0},
+      {sph_hot.data(), sph_hot.size() * 16, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -295,7 +313,7 @@ int rt_scene_upload(const rt_scene *scene) {
     CK(cudaStreamSynchronize(d.stream));
     char *b = (char *)d.scene_blob;
     DevScene &sc = d.sc;
-    sc.n_shapes = n; sc.n_spheres = (int)sph.size(); sc.n_planes = (int)pln_idx.size();
+    sc.n_shapes = n; sc.n_spheres = n_sph_real; sc.n_planes = (int)pln_idx.size();
     sc.n_quadrics = (int)quad_idx.size(); sc.n_lights = nl;
     sc.cam_w = scene->camera_width; sc.cam_h = scene->camera_height;
     sc.sph = (const float4 *)(b + secs[0].off); sc.sph_prim = (const float4 *)(b + secs[1].off);
@@ -303,6 +321,7 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.pln_idx = (const int *)(b + secs[4].off); sc.quad = (const float4 *)(b + secs[5].off);
     sc.quad_idx = (const int *)(b + secs[6].off); sc.mat = (const float4 *)(b + secs[7].off);
     sc.slot = (const int2 *)(b + secs[8].off); sc.lights = (const float4 *)(b + secs[9].off);
+    sc.sph_hot = (const float4 *)(b + secs[10].off);
   }
   g_have_scene = true;
   g_n_lights = nl;
@@ -328,6 +347,8 @@ void launch_shade(DeviceCtx &d, int grid, int level, HitQueue qin, HitQueue qout
 }
 
 int pick_lb(int n_lights) {
+  const char *e = getenv("RT_LIGHT_BATCH");   // tuning knob: lights per pass (1,2,4,8,16)
+  if (e) { int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) return v; }
   const int c[5] = {1, 2, 4, 8, 16};
   for (int v : c) if (n_lights <= v) return v;
   return 16;
@@ -394,7 +415,7 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     tg.n_px = (int)((px_total - first) < (long long)tile ? (px_total - first) : (long long)tile);
     CK(cudaMemsetAsync(d.qcount, 0, 8 * sizeof(int), d.stream));
     HitQueue q0 = q[0]; q0.count = d.qcount;
-    int gp = (tg.n_px + 255) / 256; if (gp > d.grid_primary) gp = d.grid_primary;
+    int gp = (tg.n_px + 256 * RT_PRIM_PX - 1) / (256 * RT_PRIM_PX); if (gp > d.grid_primary) gp = d.grid_primary;
     if ((mr = mark(d, 'p')) != RT_OK) return mr;
     k_primary<<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, d.counters);
     plan->launches++;

@@ -10,7 +10,11 @@
 #pragma once
 #include "rt_scene.cuh"
 
+#ifndef RT_SHADE_MINB
+#define RT_SHADE_MINB 4
+#endif
 #define RT_INF __int_as_float(0x7f800000)
+#define RT_FILTER_EPS 3.814697265625e-06f   /* 2^-18, margin of the sphere reject filter */
 
 struct TileGeom {
   int width, height;        // full image
@@ -72,6 +76,7 @@ RT_DEV void finish_hit(const DevScene &sc, v3 o, v3 d, float t, int idx, v3 &P, 
 // ---------------------------------------------------------------------------------
 // k_primary: one thread per pixel of the tile (grid-stride).
 // ---------------------------------------------------------------------------------
+#define RT_PRIM_PX 4   // pixels (= primary rays) per thread: one sphere load feeds four reject tests
 __global__ void __launch_bounds__(256)
 k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict__ c0,
           HitQueue q, unsigned long long *__restrict__ counters) {
@@ -79,68 +84,102 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
   const float ph = __fdiv_rn(sc.cam_h, (float)tg.height);   // C/raycast.c:109
   const double half_w = __ddiv_rn((double)sc.cam_w, 2.0), half_h = __ddiv_rn((double)sc.cam_h, 2.0);
   unsigned long long n_hits = 0, n_sph = 0, n_pln = 0, n_quad = 0, n_cand = 0;
-  const int stride = gridDim.x * blockDim.x;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < tg.n_px; i += stride) {
-    long long g = tg.first_px + i;
-    int lr = (int)(g / tg.width), x = (int)(g - (long long)lr * tg.width);
-    int y = local_to_image_row(lr, tg.rank, tg.nranks, tg.band_h);
-    // C/raycast.c:115-118 (double expression, float store, normalise)
-    v3 d;
-    d.x = (float)add64(sub64(0.0, half_w), mul64((double)pw, add64((double)x, 0.5)));
-    d.y = (float)sub64(add64(0.0, half_h), mul64((double)ph, add64((double)y, 0.5)));
-    d.z = -1.0f;
-    d = norm3(d);
-    const v3 o = mk3(0.0f, 0.0f, 0.0f);
-    const float a = ray_a(d);
-    float best_t = RT_INF;
-    int best_idx = -1;
-    // spheres: origin part precomputed on the host (origin is exactly 0)
-    for (int s = 0; s < sc.n_spheres; s++) {
-      float4 sp = sc.sph_prim[s];
-      float dt = dot3(d, mk3(sp.x, sp.y, sp.z));
-      float dq = __fmaf_rn(dt, dt, -mul32(a, sp.w));
-      if (dq >= 0.0f) {
-        n_cand++;
-        float t;
-        if (sphere_t_literal(o, d, sc.sph[s], t)) {
-          int idx = sc.sph_idx[s];
-          if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
+  const int stride = gridDim.x * blockDim.x * RT_PRIM_PX;
+  const v3 o = mk3(0.0f, 0.0f, 0.0f);
+  for (int base = blockIdx.x * blockDim.x * RT_PRIM_PX + threadIdx.x; base < tg.n_px; base += stride) {
+    v3 d[RT_PRIM_PX];
+    float best_t[RT_PRIM_PX];
+    int best_idx[RT_PRIM_PX];
+    unsigned live = 0;
+    #pragma unroll
+    for (int k = 0; k < RT_PRIM_PX; k++) {
+      const int i = base + k * blockDim.x;
+      best_t[k] = RT_INF; best_idx[k] = -1;
+      d[k] = mk3(0.f, 0.f, 0.f);
+      if (i < tg.n_px) {
+        live |= 1u << k;
+        long long g = tg.first_px + i;
+        int lr = (int)(g / tg.width), x = (int)(g - (long long)lr * tg.width);
+        int y = local_to_image_row(lr, tg.rank, tg.nranks, tg.band_h);
+        // C/raycast.c:115-118 (double expression, float store, normalise)
+        d[k].x = (float)add64(sub64(0.0, half_w), mul64((double)pw, add64((double)x, 0.5)));
+        d[k].y = (float)sub64(add64(0.0, half_h), mul64((double)ph, add64((double)y, 0.5)));
+        d[k].z = -1.0f;
+        d[k] = norm3(d[k]);
+      }
+    }
+    const int n_live = __popc(live);
+    // spheres: the origin is exactly (0,0,0), so tmp' = -centre and the filter constant k
+    // are per-sphere constants prepared on the host (sph_prim).
+    for (int s = 0; s < sc.n_spheres; s += 2) {
+      const float4 h0 = sc.sph_prim[s], h1 = sc.sph_prim[s + 1];
+      float m0 = -1.0f, m1 = -1.0f;
+      #pragma unroll
+      for (int k = 0; k < RT_PRIM_PX; k++) {
+        const float e0 = __fmaf_rn(d[k].z, h0.z, __fmaf_rn(d[k].y, h0.y, d[k].x * h0.x));
+        const float e1 = __fmaf_rn(d[k].z, h1.z, __fmaf_rn(d[k].y, h1.y, d[k].x * h1.x));
+        m0 = fmaxf(m0, __fmaf_rn(e0, e0, h0.w));
+        m1 = fmaxf(m1, __fmaf_rn(e1, e1, h1.w));
+      }
+      if (fmaxf(m0, m1) >= 0.0f) {
+        #pragma unroll 1
+        for (int u = 0; u < 2; u++) {
+          if ((u ? m1 : m0) < 0.0f) continue;
+          const float4 hs = u ? h1 : h0;
+          const float4 sp = sc.sph[s + u];
+          const int idx = sc.sph_idx[s + u];
+          #pragma unroll
+          for (int k = 0; k < RT_PRIM_PX; k++) {
+            const float e = __fmaf_rn(d[k].z, hs.z, __fmaf_rn(d[k].y, hs.y, d[k].x * hs.x));
+            if (__fmaf_rn(e, e, hs.w) >= 0.0f && ((live >> k) & 1u)) {
+              n_cand++;
+              float t;
+              if (sphere_t_literal(o, d[k], sp, t) && better_hit(t, idx, best_t[k], best_idx[k])) { best_t[k] = t; best_idx[k] = idx; }
+            }
+          }
         }
       }
     }
-    n_sph += sc.n_spheres;
+    n_sph += (unsigned long long)sc.n_spheres * n_live;
     for (int p = 0; p < sc.n_planes; p++) {
       float4 pp = sc.pln[2 * p], pn = sc.pln[2 * p + 1];
       v3 n = mk3(pn.x, pn.y, pn.z);
       float num = dot3(sub3(o, mk3(pp.x, pp.y, pp.z)), n);
-      float t;
-      if (plane_t(num, d, n, t)) {
-        int idx = sc.pln_idx[p];
-        if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
+      int idx = sc.pln_idx[p];
+      #pragma unroll
+      for (int k = 0; k < RT_PRIM_PX; k++) {
+        float t;
+        if (((live >> k) & 1u) && plane_t(num, d[k], n, t) && better_hit(t, idx, best_t[k], best_idx[k])) { best_t[k] = t; best_idx[k] = idx; }
       }
     }
-    n_pln += sc.n_planes;
-    for (int k = 0; k < sc.n_quadrics; k++) {
-      quad10 qq = load_quad(sc.quad, k);
+    n_pln += (unsigned long long)sc.n_planes * n_live;
+    for (int kq = 0; kq < sc.n_quadrics; kq++) {
+      quad10 qq = load_quad(sc.quad, kq);
       float c_q = (float)quadric_cq(o, qq);
-      float t;
-      if (quadric_t(o, d, qq, c_q, t)) { // skip_index == -1: no z rule on primary rays
-        int idx = sc.quad_idx[k];
-        if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
+      int idx = sc.quad_idx[kq];
+      #pragma unroll 1
+      for (int k = 0; k < RT_PRIM_PX; k++) {
+        float t;   // skip_index == -1: no z rule on primary rays
+        if (((live >> k) & 1u) && quadric_t(o, d[k], qq, c_q, t) && better_hit(t, idx, best_t[k], best_idx[k])) { best_t[k] = t; best_idx[k] = idx; }
       }
     }
-    n_quad += sc.n_quadrics;
-    acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (best_idx < 0) {
-      c0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    } else {
-      n_hits++;
-      v3 P, N;
-      finish_hit(sc, o, d, best_t, best_idx, P, N);
-      int slot = queue_push_slot(q.count);
-      q.r0[slot] = make_float4(P.x, P.y, P.z, __int_as_float(i));
-      q.r1[slot] = make_float4(N.x, N.y, N.z, __int_as_float(best_idx));
-      q.r2[slot] = make_float4(d.x, d.y, d.z, 1.0f);
+    n_quad += (unsigned long long)sc.n_quadrics * n_live;
+    #pragma unroll
+    for (int k = 0; k < RT_PRIM_PX; k++) {
+      const int i = base + k * blockDim.x;
+      if (i >= tg.n_px) continue;
+      acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (best_idx[k] < 0) {
+        c0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        n_hits++;
+        v3 P, N;
+        finish_hit(sc, o, d[k], best_t[k], best_idx[k], P, N);
+        int slot = queue_push_slot(q.count);
+        q.r0[slot] = make_float4(P.x, P.y, P.z, __int_as_float(i));
+        q.r1[slot] = make_float4(N.x, N.y, N.z, __int_as_float(best_idx[k]));
+        q.r2[slot] = make_float4(d[k].x, d[k].y, d[k].z, 1.0f);
+      }
     }
   }
   // counters: one atomic per warp per counter
@@ -170,12 +209,13 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
 // part (sphere: tmp, c; plane: num; quadric: c_q) is computed once.
 // ---------------------------------------------------------------------------------
 template <int LB>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, RT_SHADE_MINB)
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
         float4 *__restrict__ c0, unsigned long long *__restrict__ counters) {
   constexpr int NR = LB + 1;
-  unsigned long long n_refl = 0, n_shadow = 0, n_hp = 0, n_so = 0, n_sd = 0, n_po = 0, n_pd = 0,
-                     n_qo = 0, n_qd = 0, n_ls = 0, n_cand = 0;
+  // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
+  // counters are products of these with the scene's primitive counts, formed at the end
+  unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_live_sum = 0, n_ls = 0, n_cand = 0;
   const int n_items = *qin.count;
   const int stride = gridDim.x * blockDim.x;
   for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < n_items; item += stride) {
@@ -189,7 +229,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
     const bool lit = opacity > 0.0f;                         // C/raycast.c:385
     n_hp++;
     if (need_refl) n_refl++;
-    if (lit) n_shadow += sc.n_lights;
+    if (lit) n_lit++;
 
     v3 rd = mk3(0.f, 0.f, 0.f);
     if (need_refl) rd = norm3(reflect3(V, N));               // C/raycast.c:353-355
@@ -201,43 +241,54 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
     for (int pass = 0; pass < n_pass; pass++) {
       // ---- ray setup -------------------------------------------------------------
       v3 d[NR];
-      float a[NR];
       unsigned alive = 0;
-      d[0] = mk3(0.f, 0.f, 0.f); a[0] = 1.0f;
-      if (need_refl && pass == 0) { d[0] = rd; a[0] = ray_a(rd); alive |= 1u; }
+      d[0] = mk3(0.f, 0.f, 0.f);
+      if (need_refl && pass == 0) { d[0] = rd; alive |= 1u; }
       #pragma unroll
       for (int j = 1; j < NR; j++) {
         int l = pass * LB + j - 1;
-        d[j] = mk3(0.f, 0.f, 0.f); a[j] = 1.0f;
+        d[j] = mk3(0.f, 0.f, 0.f);
         if (lit && l < sc.n_lights) {
           float4 lp = sc.lights[4 * l];
           d[j] = norm3(sub3(mk3(lp.x, lp.y, lp.z), P));     // C/raycast.c:396-398
-          a[j] = ray_a(d[j]);
           alive |= 1u << j;
         }
       }
-      const int n_live = __popc(alive);
+      n_live_sum += __popc(alive); n_pass_sum++;
       // ---- spheres ---------------------------------------------------------------
-      #pragma unroll 2
-      for (int s = 0; s < sc.n_spheres; s++) {
-        const float4 sp = sc.sph[s];
-        const v3 tmp = sub3(P, mk3(sp.x, sp.y, sp.z));
-        const float c = __fmaf_rn(-sp.w, sp.w, dot3(tmp, tmp));
-        float m = -1.0f;
+      // Hot loop = the conservative FP32/FMA reject filter (DESIGN.md "sphere filter"):
+      //   q' = fma(dt', dt', k),  dt' = fma-chain dot(d, tmp'),  k = 2^-18 (T' + r^2) - (T' - r^2)
+      // q' < 0 proves the reference's discriminant (C/raycast.c:587) negative, so the ray
+      // misses; everything else goes to the literal intersection, which decides alone.
+      // Two spheres per trip (arrays are padded to an even count with never-passing entries).
+      for (int s = 0; s < sc.n_spheres; s += 2) {
+        const float4 h0 = sc.sph_hot[s], h1 = sc.sph_hot[s + 1];
+        const float x0 = P.x - h0.x, y0 = P.y - h0.y, z0 = P.z - h0.z;
+        const float x1 = P.x - h1.x, y1 = P.y - h1.y, z1 = P.z - h1.z;
+        const float T0 = __fmaf_rn(z0, z0, __fmaf_rn(y0, y0, x0 * x0));
+        const float T1 = __fmaf_rn(z1, z1, __fmaf_rn(y1, y1, x1 * x1));
+        const float k0 = __fmaf_rn(RT_FILTER_EPS, T0 + h0.w, h0.w - T0);
+        const float k1 = __fmaf_rn(RT_FILTER_EPS, T1 + h1.w, h1.w - T1);
+        float m0 = -1.0f, m1 = -1.0f;
         #pragma unroll
         for (int j = 0; j < NR; j++) {
-          float dt = dot3(d[j], tmp);
-          float dq = __fmaf_rn(dt, dt, -mul32(a[j], c));
-          m = fmaxf(m, dq);
+          const float e0 = __fmaf_rn(d[j].z, z0, __fmaf_rn(d[j].y, y0, d[j].x * x0));
+          const float e1 = __fmaf_rn(d[j].z, z1, __fmaf_rn(d[j].y, y1, d[j].x * x1));
+          m0 = fmaxf(m0, __fmaf_rn(e0, e0, k0));
+          m1 = fmaxf(m1, __fmaf_rn(e1, e1, k1));
         }
-        if (m >= 0.0f) {
-          const int idx = sc.sph_idx[s];
-          if (idx != obj) {                                  // C/raycast.c:450
+        if (fmaxf(m0, m1) >= 0.0f) {
+          #pragma unroll 1
+          for (int u = 0; u < 2; u++) {
+            if ((u ? m1 : m0) < 0.0f) continue;
+            const int idx = sc.sph_idx[s + u];
+            if (idx == obj) continue;                          // C/raycast.c:450
+            const float4 sp = sc.sph[s + u];
+            const float xs = u ? x1 : x0, ys = u ? y1 : y0, zs = u ? z1 : z0, ks = u ? k1 : k0;
             #pragma unroll
             for (int j = 0; j < NR; j++) {
-              float dt = dot3(d[j], tmp);
-              float dq = __fmaf_rn(dt, dt, -mul32(a[j], c));
-              if (dq >= 0.0f && ((alive >> j) & 1u)) {
+              const float e = __fmaf_rn(d[j].z, zs, __fmaf_rn(d[j].y, ys, d[j].x * xs));
+              if (__fmaf_rn(e, e, ks) >= 0.0f && ((alive >> j) & 1u)) {
                 n_cand++;
                 float t;
                 if (sphere_t_literal(P, d[j], sp, t)) {
@@ -249,7 +300,6 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
           }
         }
       }
-      n_so += sc.n_spheres; n_sd += (unsigned long long)sc.n_spheres * n_live;
       // ---- planes ----------------------------------------------------------------
       for (int p = 0; p < sc.n_planes; p++) {
         const int idx = sc.pln_idx[p];
@@ -266,7 +316,6 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
           }
         }
       }
-      n_po += sc.n_planes; n_pd += (unsigned long long)sc.n_planes * n_live;
       // ---- quadrics --------------------------------------------------------------
       for (int k = 0; k < sc.n_quadrics; k++) {
         const int idx = sc.quad_idx[k];
@@ -283,7 +332,6 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
           }
         }
       }
-      n_qo += sc.n_quadrics; n_qd += (unsigned long long)sc.n_quadrics * n_live;
       // ---- Phong for the lights of this pass that stayed unoccluded, in light order
       #pragma unroll
       for (int j = 1; j < NR; j++) {
@@ -341,14 +389,30 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
       qout.r2[slot] = make_float4(rd.x, rd.y, rd.z, mul32(tr, refl));   // total_refl, :345,362
     }
   }
-  unsigned long long v[11] = {n_refl, n_shadow, n_hp, n_so, n_sd, n_po, n_pd, n_qo, n_qd, n_ls, n_cand};
-  const int where[11] = {CT_RAYS_REFLECTION, CT_RAYS_SHADOW, CT_HIT_POINTS, CT_SPH_O, CT_SPH_D, CT_PLN_O,
-                         CT_PLN_D, CT_QUAD_O, CT_QUAD_D, CT_LIGHT_SAMPLES, CT_CANDIDATES};
+  unsigned v[7] = {n_refl, n_lit, n_hp, n_pass_sum, n_live_sum, n_ls, n_cand};
   #pragma unroll
-  for (int k = 0; k < 11; k++) {
+  for (int k = 0; k < 7; k++) {
     #pragma unroll
     for (int off = 16; off; off >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
-    if ((threadIdx.x & 31) == 0 && v[k]) atomicAdd(&counters[where[k]], v[k]);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    typedef unsigned long long u64;
+    const u64 ns = sc.n_spheres, np = sc.n_planes, nq = sc.n_quadrics;
+    if (v[0]) atomicAdd(&counters[CT_RAYS_REFLECTION], (u64)v[0]);
+    if (v[1]) atomicAdd(&counters[CT_RAYS_SHADOW], (u64)v[1] * sc.n_lights);
+    if (v[2]) atomicAdd(&counters[CT_HIT_POINTS], (u64)v[2]);
+    if (v[3]) {
+      if (ns) atomicAdd(&counters[CT_SPH_O], v[3] * ns);
+      if (np) atomicAdd(&counters[CT_PLN_O], v[3] * np);
+      if (nq) atomicAdd(&counters[CT_QUAD_O], v[3] * nq);
+    }
+    if (v[4]) {
+      if (ns) atomicAdd(&counters[CT_SPH_D], v[4] * ns);
+      if (np) atomicAdd(&counters[CT_PLN_D], v[4] * np);
+      if (nq) atomicAdd(&counters[CT_QUAD_D], v[4] * nq);
+    }
+    if (v[5]) atomicAdd(&counters[CT_LIGHT_SAMPLES], (u64)v[5]);
+    if (v[6]) atomicAdd(&counters[CT_CANDIDATES], (u64)v[6]);
   }
 }
 

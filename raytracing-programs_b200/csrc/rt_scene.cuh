@@ -11,6 +11,7 @@ struct DevScene {
   int n_shapes, n_spheres, n_planes, n_quadrics, n_lights;
   float cam_w, cam_h;
   const float4 *sph;        // [n_spheres] {cx, cy, cz, r}
+  const float4 *sph_hot;    // [n_spheres padded to 4] reject-filter operands {cx, cy, cz, fl(r*r)}; pads never pass
   const float4 *sph_prim;   // [n_spheres] primary-ray constants {0-cx, 0-cy, 0-cz, c} (origin is exactly 0)
   const int *sph_idx;       // [n_spheres] original index
   const float4 *pln;        // [2*n_planes] {px,py,pz,0} {nx,ny,nz,0}
