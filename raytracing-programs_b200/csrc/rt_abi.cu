@@ -281,7 +281,8 @@ int rt_scene_upload(const rt_scene *scene) {
   }
   // pad the per-sphere arrays to a multiple of 4 with entries the reject filter never passes
   // (r*r = -inf => k = -inf) so the hot loops can run unrolled without a tail
-  while (sph_hot.size() % 4) {
+  const size_t padded = (sph_hot.size() + 3) / 4 * 4 + 4;   // + one prefetch group
+  while (sph_hot.size() < padded) {
     sph_hot.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));
     sph.push_back(make_float4(0.f, 0.f, 0.f, 0.f));
     sph_prim.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));

@@ -13,6 +13,7 @@
 #ifndef RT_SHADE_MINB
 #define RT_SHADE_MINB 4
 #endif
+#define RT_CHUNK 128     /* spheres per scan chunk = capacity of the per-thread survivor queue */
 #define RT_INF __int_as_float(0x7f800000)
 #define RT_FILTER_EPS 3.814697265625e-06f   /* 2^-18, margin of the sphere reject filter */
 
@@ -213,6 +214,9 @@ __global__ void __launch_bounds__(128, RT_SHADE_MINB)
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
         float4 *__restrict__ c0, unsigned long long *__restrict__ counters) {
   constexpr int NR = LB + 1;
+  __shared__ unsigned char cand[RT_CHUNK][128];
+  __shared__ float dsm[3 * NR][128];
+  const int tid = threadIdx.x;
   // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
   // counters are products of these with the scene's primitive counts, formed at the end
   unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_live_sum = 0, n_ls = 0, n_cand = 0;
@@ -239,80 +243,122 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
 
     const int n_pass = (sc.n_lights + LB - 1) / LB > 0 ? (sc.n_lights + LB - 1) / LB : 1;
     for (int pass = 0; pass < n_pass; pass++) {
-      // ---- ray setup -------------------------------------------------------------
-      v3 d[NR];
+      // ---- ray setup: registers for the sphere scan, a shared-memory copy (dsm) for the
+      // compact run-time-indexed loops (survivors, planes, quadrics, Phong) ----------
       unsigned alive = 0;
-      d[0] = mk3(0.f, 0.f, 0.f);
-      if (need_refl && pass == 0) { d[0] = rd; alive |= 1u; }
-      #pragma unroll
+      {
+        const bool r_on = need_refl && pass == 0;
+        dsm[0][tid] = r_on ? rd.x : 0.f; dsm[1][tid] = r_on ? rd.y : 0.f; dsm[2][tid] = r_on ? rd.z : 0.f;
+        alive = r_on ? 1u : 0u;
+      }
+      #pragma unroll 1
       for (int j = 1; j < NR; j++) {
-        int l = pass * LB + j - 1;
-        d[j] = mk3(0.f, 0.f, 0.f);
+        const int l = pass * LB + j - 1;
+        v3 dj = mk3(0.f, 0.f, 0.f);
         if (lit && l < sc.n_lights) {
-          float4 lp = sc.lights[4 * l];
-          d[j] = norm3(sub3(mk3(lp.x, lp.y, lp.z), P));     // C/raycast.c:396-398
+          const float4 lp = sc.lights[4 * l];
+          dj = norm3(sub3(mk3(lp.x, lp.y, lp.z), P));       // C/raycast.c:396-398
           alive |= 1u << j;
         }
+        dsm[3 * j][tid] = dj.x; dsm[3 * j + 1][tid] = dj.y; dsm[3 * j + 2][tid] = dj.z;
       }
+      v3 d[NR];
+      #pragma unroll
+      for (int j = 0; j < NR; j++) d[j] = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
       n_live_sum += __popc(alive); n_pass_sum++;
       // ---- spheres ---------------------------------------------------------------
-      // Hot loop = the conservative FP32/FMA reject filter (DESIGN.md "sphere filter"):
-      //   q' = fma(dt', dt', k),  dt' = fma-chain dot(d, tmp'),  k = 2^-18 (T' + r^2) - (T' - r^2)
-      // q' < 0 proves the reference's discriminant (C/raycast.c:587) negative, so the ray
-      // misses; everything else goes to the literal intersection, which decides alone.
-      // Two spheres per trip (arrays are padded to an even count with never-passing entries).
-      for (int s = 0; s < sc.n_spheres; s += 2) {
-        const float4 h0 = sc.sph_hot[s], h1 = sc.sph_hot[s + 1];
-        const float x0 = P.x - h0.x, y0 = P.y - h0.y, z0 = P.z - h0.z;
-        const float x1 = P.x - h1.x, y1 = P.y - h1.y, z1 = P.z - h1.z;
-        const float T0 = __fmaf_rn(z0, z0, __fmaf_rn(y0, y0, x0 * x0));
-        const float T1 = __fmaf_rn(z1, z1, __fmaf_rn(y1, y1, x1 * x1));
-        const float k0 = __fmaf_rn(RT_FILTER_EPS, T0 + h0.w, h0.w - T0);
-        const float k1 = __fmaf_rn(RT_FILTER_EPS, T1 + h1.w, h1.w - T1);
-        float m0 = -1.0f, m1 = -1.0f;
-        #pragma unroll
-        for (int j = 0; j < NR; j++) {
-          const float e0 = __fmaf_rn(d[j].z, z0, __fmaf_rn(d[j].y, y0, d[j].x * x0));
-          const float e1 = __fmaf_rn(d[j].z, z1, __fmaf_rn(d[j].y, y1, d[j].x * x1));
-          m0 = fmaxf(m0, __fmaf_rn(e0, e0, k0));
-          m1 = fmaxf(m1, __fmaf_rn(e1, e1, k1));
+      // Scan = conservative reject filter (DESIGN.md "sphere filter").  With tmp' = P - C,
+      // e_j = fma-chain dot(d_j, tmp'), T' = |tmp'|^2, kappa = (T' - r^2) - 2^-18 (T' + r^2):
+      //   max_j e_j^2 < kappa  proves the reference's discriminant (C/raycast.c:587) negative
+      //   for every ray leaving P, so none of them hits this sphere.
+      // Survivors of one chunk of RT_CHUNK spheres are queued per thread in shared memory
+      // and resolved after the chunk, so the scan never diverges.  Two spheres per trip;
+      // the arrays are padded with entries that never pass (r^2 = -inf => kappa = +inf).
+      for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
+        const int ce = min(cs + RT_CHUNK, sc.n_spheres);
+        int nc = 0;
+        float4 h0 = sc.sph_hot[cs], h1 = sc.sph_hot[cs + 1];
+        for (int s = cs; s < ce; s += 2) {
+          const float4 g0 = h0, g1 = h1;
+          h0 = sc.sph_hot[s + 2]; h1 = sc.sph_hot[s + 3];      // prefetch (4 spare entries at the end)
+          const float x0 = P.x - g0.x, y0 = P.y - g0.y, z0 = P.z - g0.z;
+          const float x1 = P.x - g1.x, y1 = P.y - g1.y, z1 = P.z - g1.z;
+          const float T0 = __fmaf_rn(z0, z0, __fmaf_rn(y0, y0, x0 * x0));
+          const float T1 = __fmaf_rn(z1, z1, __fmaf_rn(y1, y1, x1 * x1));
+          const float ka0 = __fmaf_rn(-RT_FILTER_EPS, T0 + g0.w, T0 - g0.w);
+          const float ka1 = __fmaf_rn(-RT_FILTER_EPS, T1 + g1.w, T1 - g1.w);
+          float mx0 = 0.0f, mx1 = 0.0f;
+          #pragma unroll
+          for (int j = 0; j < NR; j++) {
+            mx0 = fmaxf(mx0, fabsf(__fmaf_rn(d[j].z, z0, __fmaf_rn(d[j].y, y0, d[j].x * x0))));
+            mx1 = fmaxf(mx1, fabsf(__fmaf_rn(d[j].z, z1, __fmaf_rn(d[j].y, y1, d[j].x * x1))));
+          }
+          const bool pass0 = mx0 * mx0 >= ka0, pass1 = mx1 * mx1 >= ka1;
+          if (pass0 || pass1) {
+            if (pass0) cand[nc++][tid] = (unsigned char)(s - cs);
+            if (pass1) cand[nc++][tid] = (unsigned char)(s + 1 - cs);
+          }
         }
-        if (fmaxf(m0, m1) >= 0.0f) {
-          #pragma unroll 1
-          for (int u = 0; u < 2; u++) {
-            if ((u ? m1 : m0) < 0.0f) continue;
-            const int idx = sc.sph_idx[s + u];
-            if (idx == obj) continue;                          // C/raycast.c:450
-            const float4 sp = sc.sph[s + u];
-            const float xs = u ? x1 : x0, ys = u ? y1 : y0, zs = u ? z1 : z0, ks = u ? k1 : k0;
-            #pragma unroll
-            for (int j = 0; j < NR; j++) {
-              const float e = __fmaf_rn(d[j].z, zs, __fmaf_rn(d[j].y, ys, d[j].x * xs));
-              if (__fmaf_rn(e, e, ks) >= 0.0f && ((alive >> j) & 1u)) {
-                n_cand++;
-                float t;
-                if (sphere_t_literal(P, d[j], sp, t)) {
-                  if (j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
-                  else if (t > 0.0f && t < RT_INF) alive &= ~(1u << j);
-                }
+        // ---- resolve the survivors of this chunk ---------------------------------
+        for (int i = 0; i < nc; i++) {
+          const int ss = cs + cand[i][tid];
+          const int idx = sc.sph_idx[ss];
+          if (idx == obj) continue;                            // C/raycast.c:450
+          const float4 hh = sc.sph_hot[ss];
+          const float xs = P.x - hh.x, ys = P.y - hh.y, zs = P.z - hh.z;
+          const float Ts = __fmaf_rn(zs, zs, __fmaf_rn(ys, ys, xs * xs));
+          const float cp = Ts - hh.w, marg = RT_FILTER_EPS * (Ts + hh.w);
+          const float lo = cp - marg, hi = cp + marg;
+          unsigned pm = 0;
+          #pragma unroll
+          for (int j = 0; j < NR; j++) {
+            const float e = __fmaf_rn(d[j].z, zs, __fmaf_rn(d[j].y, ys, d[j].x * xs));
+            pm |= (unsigned)(e * e >= lo) << j;
+          }
+          for (pm &= alive; pm; pm &= pm - 1) {
+            const int j = __ffs(pm) - 1;
+            const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+            const float e = __fmaf_rn(dj.z, zs, __fmaf_rn(dj.y, ys, dj.x * xs));
+            const float e2 = e * e;
+            // Sign analysis: with the discriminant certainly >= 0 (e2 >= hi, or
+            // the origin certainly inside) and c certainly away from 0 relative to e2, the
+            // reference's root selection (C/raycast.c:593-597) yields t > 0 exactly when the
+            // origin is inside, or outside with the sphere ahead (dt < 0).  A shadow ray
+            // needs no root then; whatever is uncertain takes the literal path.
+            const float guard = 1.52587890625e-05f * e2;       // 2^-16 e^2
+            const bool inside = cp <= -(marg + guard);
+            const bool outside = (cp >= marg + guard) && (e2 >= hi);
+            const bool need_lit = (j == 0) ? !(outside && e > 0.0f) : !(inside || outside);
+            bool occl = (j != 0) && (inside || (outside && e < 0.0f));
+            if (need_lit) {
+              n_cand++;
+              float t;
+              if (sphere_t_literal(P, dj, sc.sph[ss], t)) {
+                if (j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
+                else occl = (t > 0.0f) && (t < RT_INF);
               }
             }
+            if (occl) alive &= ~(1u << j);
           }
         }
       }
       // ---- planes ----------------------------------------------------------------
+      // t = (-1*num)/den as the reference computes it (C/raycast.c:545-562): den == 0 or
+      // t < 0 is a miss, and a hit counts only with 0 < t < inf (:476).
       for (int p = 0; p < sc.n_planes; p++) {
         const int idx = sc.pln_idx[p];
-        if (idx == obj) continue;
+        if (idx == obj) continue;                              // C/raycast.c:450
         const float4 pp = sc.pln[2 * p], pn = sc.pln[2 * p + 1];
         const v3 n = mk3(pn.x, pn.y, pn.z);
-        const float num = dot3(sub3(P, mk3(pp.x, pp.y, pp.z)), n);
-        #pragma unroll
-        for (int j = 0; j < NR; j++) {
-          float t;
-          if (((alive >> j) & 1u) && plane_t(num, d[j], n, t)) {
+        const float nn = mul32(-1.0f, dot3(sub3(P, mk3(pp.x, pp.y, pp.z)), n));
+        for (unsigned m = alive; m; m &= m - 1) {
+          const int j = __ffs(m) - 1;
+          const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+          const float den = dot3(dj, n);
+          const float t = __fdiv_rn(nn, den);
+          if (den != 0.0f && t > 0.0f && t < RT_INF) {
             if (j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
-            else if (t > 0.0f && t < RT_INF) alive &= ~(1u << j);
+            else alive &= ~(1u << j);
           }
         }
       }
@@ -322,25 +368,25 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
         if (idx == obj) continue;
         const quad10 qq = load_quad(sc.quad, k);
         const float c_q = (float)quadric_cq(P, qq);
-        #pragma unroll
-        for (int j = 0; j < NR; j++) {
+        for (unsigned m = alive; m; m &= m - 1) {
+          const int j = __ffs(m) - 1;
+          const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
           float t;
-          if (((alive >> j) & 1u) && quadric_t(P, d[j], qq, c_q, t)) {
-            if (add32(P.z, mul32(t, d[j].z)) < P.z) continue;   // C/raycast.c:492-494 (skip_index != -1 here)
+          if (quadric_t(P, dj, qq, c_q, t)) {
+            if (add32(P.z, mul32(t, dj.z)) < P.z) continue;   // C/raycast.c:492-494 (skip_index != -1 here)
             if (j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
             else if (t > 0.0f && t < RT_INF) alive &= ~(1u << j);
           }
         }
       }
       // ---- Phong for the lights of this pass that stayed unoccluded, in light order
-      #pragma unroll
-      for (int j = 1; j < NR; j++) {
-        if (!((alive >> j) & 1u)) continue;
+      for (unsigned m = alive & ~1u; m; m &= m - 1) {
+        const int j = __ffs(m) - 1;
         n_ls++;
         const int l = pass * LB + j - 1;
         const float4 l0 = sc.lights[4 * l], l1 = sc.lights[4 * l + 1], l2 = sc.lights[4 * l + 2];
         const v3 Lpos = mk3(l0.x, l0.y, l0.z);
-        const v3 Ld = d[j];
+        const v3 Ld = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
         const float dist = len3(sub3(Lpos, P));              // C/raycast.c:397
         // radial_attenuation, C/raycast.c:666-669
         const float rad = (float)__ddiv_rn(1.0, add64((double)add32(l2.x, mul32(l2.y, dist)),
