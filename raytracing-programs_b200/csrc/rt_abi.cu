@@ -54,7 +54,7 @@ struct DeviceCtx {
   size_t tile_cap = 0;
   float4 *acc = nullptr, *c0 = nullptr;
   float4 *qbuf = nullptr;     // 6 * tile_cap float4: two queues x {r0,r1,r2}
-  int *qcount = nullptr;      // 8 ints: one count per wavefront level (+1 spare)
+  int *qcount = nullptr;      // 16 ints: [0..7] one count per wavefront level (+1 spare), [8..15] work cursors
   unsigned long long *counters = nullptr;
   // output
   uint8_t *rank_buf = nullptr; size_t rank_cap = 0;
@@ -205,7 +205,7 @@ int rt_init(int n_gpus) {
     d.sm_count = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
-    CK(cudaMalloc((void **)&d.qcount, 8 * sizeof(int)));
+    CK(cudaMalloc((void **)&d.qcount, 16 * sizeof(int)));
     CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
   }
   g_ndev = n;
@@ -403,7 +403,7 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     q[k].r0 = d.qbuf + (size_t)(3 * k) * d.tile_cap;
     q[k].r1 = d.qbuf + (size_t)(3 * k + 1) * d.tile_cap;
     q[k].r2 = d.qbuf + (size_t)(3 * k + 2) * d.tile_cap;
-    q[k].count = nullptr;
+    q[k].count = nullptr; q[k].cursor = nullptr;
   }
   CK(cudaMemsetAsync(d.counters, 0, CT_COUNT * sizeof(unsigned long long), d.stream));
   d.evkind.clear();
@@ -414,7 +414,7 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     tg.width = W; tg.height = H; tg.rank = rank; tg.nranks = nranks; tg.band_h = bh;
     tg.first_px = first;
     tg.n_px = (int)((px_total - first) < (long long)tile ? (px_total - first) : (long long)tile);
-    CK(cudaMemsetAsync(d.qcount, 0, 8 * sizeof(int), d.stream));
+    CK(cudaMemsetAsync(d.qcount, 0, 16 * sizeof(int), d.stream));
     HitQueue q0 = q[0]; q0.count = d.qcount;
     int gp = (tg.n_px + 256 * RT_PRIM_PX - 1) / (256 * RT_PRIM_PX); if (gp > d.grid_primary) gp = d.grid_primary;
     if ((mr = mark(d, 'p')) != RT_OK) return mr;
@@ -423,6 +423,7 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     for (int level = 0; level < 7; level++) {
       HitQueue qin = q[level & 1], qout = q[(level + 1) & 1];
       qin.count = d.qcount + level; qout.count = d.qcount + level + 1;
+      qin.cursor = d.qcount + 8 + level; qout.cursor = nullptr;
       if ((mr = mark(d, 's')) != RT_OK) return mr;
       switch (lb) {
         case 1: launch_shade<1>(d, d.grid_shade, level, qin, qout); break;
@@ -640,7 +641,7 @@ int rt_init_device(int ordinal) {
   d.sm_count = prop.multiProcessorCount;
   CK(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
-  CK(cudaMalloc((void **)&d.qcount, 8 * sizeof(int)));
+  CK(cudaMalloc((void **)&d.qcount, 16 * sizeof(int)));
   CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
   g_ndev = 1;
   return RT_OK;

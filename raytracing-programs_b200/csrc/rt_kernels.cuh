@@ -214,15 +214,22 @@ __global__ void __launch_bounds__(128, RT_SHADE_MINB)
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
         float4 *__restrict__ c0, unsigned long long *__restrict__ counters) {
   constexpr int NR = LB + 1;
-  __shared__ unsigned char cand[RT_CHUNK][128];
+  __shared__ unsigned char cand[RT_CHUNK + 1][128];   // +1: the branch-free push stores before it knows
   __shared__ float dsm[3 * NR][128];
   const int tid = threadIdx.x;
   // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
   // counters are products of these with the scene's primitive counts, formed at the end
   unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_live_sum = 0, n_ls = 0, n_cand = 0;
   const int n_items = *qin.count;
-  const int stride = gridDim.x * blockDim.x;
-  for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < n_items; item += stride) {
+  // Dynamic scheduling: every warp claims 32 consecutive queue entries at a time, so no SM
+  // idles while another still holds a backlog of expensive hit points.
+  for (;;) {
+    int item = 0;
+    if ((threadIdx.x & 31) == 0) item = atomicAdd(qin.cursor, 32);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= n_items) break;
+    item += threadIdx.x & 31;
+    if (item >= n_items) continue;
     const float4 r0 = qin.r0[item], r1 = qin.r1[item], r2 = qin.r2[item];
     const v3 P = mk3(r0.x, r0.y, r0.z), N = mk3(r1.x, r1.y, r1.z), V = mk3(r2.x, r2.y, r2.z);
     const int pix = __float_as_int(r0.w), obj = __float_as_int(r1.w);
@@ -276,11 +283,10 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
       // the arrays are padded with entries that never pass (r^2 = -inf => kappa = +inf).
       for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
         const int ce = min(cs + RT_CHUNK, sc.n_spheres);
-        int nc = 0;
-        float4 h0 = sc.sph_hot[cs], h1 = sc.sph_hot[cs + 1];
-        for (int s = cs; s < ce; s += 2) {
-          const float4 g0 = h0, g1 = h1;
-          h0 = sc.sph_hot[s + 2]; h1 = sc.sph_hot[s + 3];      // prefetch (4 spare entries at the end)
+        // The survivor queue is written without a branch: the slot is always stored, the
+        // queue pointer advances only when the sphere survived.
+        unsigned char *qp = &cand[0][tid];
+        auto scan_pair = [&](const float4 g0, const float4 g1, const int rel) {
           const float x0 = P.x - g0.x, y0 = P.y - g0.y, z0 = P.z - g0.z;
           const float x1 = P.x - g1.x, y1 = P.y - g1.y, z1 = P.z - g1.z;
           const float T0 = __fmaf_rn(z0, z0, __fmaf_rn(y0, y0, x0 * x0));
@@ -293,12 +299,24 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
             mx0 = fmaxf(mx0, fabsf(__fmaf_rn(d[j].z, z0, __fmaf_rn(d[j].y, y0, d[j].x * x0))));
             mx1 = fmaxf(mx1, fabsf(__fmaf_rn(d[j].z, z1, __fmaf_rn(d[j].y, y1, d[j].x * x1))));
           }
-          const bool pass0 = mx0 * mx0 >= ka0, pass1 = mx1 * mx1 >= ka1;
-          if (pass0 || pass1) {
-            if (pass0) cand[nc++][tid] = (unsigned char)(s - cs);
-            if (pass1) cand[nc++][tid] = (unsigned char)(s + 1 - cs);
-          }
+          *qp = (unsigned char)rel;
+          qp += (mx0 * mx0 >= ka0) ? 128 : 0;
+          *qp = (unsigned char)(rel + 1);
+          qp += (mx1 * mx1 >= ka1) ? 128 : 0;
+        };
+        const float4 *hp = sc.sph_hot + cs;
+        float4 a0 = hp[0], a1 = hp[1], b0 = hp[2], b1 = hp[3];
+        #pragma unroll 1
+        for (int s = cs; s < ce; s += 4) {
+          hp += 4;
+          const float4 u0 = a0, u1 = a1;
+          a0 = hp[0]; a1 = hp[1];                              // next trip's operands (4 spare entries at the end)
+          scan_pair(u0, u1, s - cs);
+          const float4 w0 = b0, w1 = b1;
+          b0 = hp[2]; b1 = hp[3];
+          scan_pair(w0, w1, s - cs + 2);
         }
+        const int nc = (int)(qp - &cand[0][tid]) >> 7;
         // ---- resolve the survivors of this chunk ---------------------------------
         for (int i = 0; i < nc; i++) {
           const int ss = cs + cand[i][tid];
@@ -355,10 +373,22 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
           const int j = __ffs(m) - 1;
           const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
           const float den = dot3(dj, n);
-          const float t = __fdiv_rn(nn, den);
-          if (den != 0.0f && t > 0.0f && t < RT_INF) {
-            if (j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
-            else alive &= ~(1u << j);
+          if (j == 0) {
+            const float t = __fdiv_rn(nn, den);
+            if (den != 0.0f && better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
+          } else {
+            // A shadow ray only asks whether 0 < t < inf.  The sign of an IEEE quotient is
+            // exact, so with both magnitudes in [2^-40, 2^40] (no underflow to 0, no overflow
+            // to inf) that is "nn and den have the same sign"; otherwise divide.
+            const float an = fabsf(nn), ad = fabsf(den);
+            bool hit;
+            if (an >= 9.094947017729282e-13f && an <= 1.099511627776e12f && ad >= 9.094947017729282e-13f && ad <= 1.099511627776e12f)
+              hit = (nn > 0.0f) == (den > 0.0f);
+            else {
+              const float t = __fdiv_rn(nn, den);
+              hit = den != 0.0f && t > 0.0f && t < RT_INF;
+            }
+            if (hit) alive &= ~(1u << j);
           }
         }
       }

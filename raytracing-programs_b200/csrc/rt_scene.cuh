@@ -29,6 +29,7 @@ struct HitQueue {
   float4 *r1;   // N.xyz, object (original index, int bits)
   float4 *r2;   // V.xyz (direction of the ray that made the hit), throughput
   int *count;
+  int *cursor;  // work cursor of the launch that consumes this queue (warps claim 32 entries at a time)
 };
 
 // Device counters (unsigned long long each).
