@@ -179,12 +179,9 @@ def main():
     r.upload(sc)
     pk = peaks()
 
-    my_rows = len(pkg.rank_rows(H, rank, world))
-    my_bytes = my_rows * W * 3
-    sizes = [len(pkg.rank_rows(H, k, world)) * W * 3 for k in range(world)]
-    offs = [0]
-    for s in sizes[:-1]:
-        offs.append(offs[-1] + ((s + 255) // 256) * 256)
+    bands = importlib.import_module("raytracing-programs_b200.bands")
+    sizes, offs = bands.layout(W, H, world)
+    my_bytes = sizes[rank]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
     rank_buf = torch.empty(my_bytes + 256, dtype=torch.uint8, device=dev)
     staging = frame = host_frame = None
@@ -203,13 +200,8 @@ def main():
         """Band gather: every rank's rows to rank 0 over NCCL (NVLink), then de-interleave."""
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        if rank == 0:
-            staging[:sizes[0]].copy_(rank_buf[:sizes[0]])
-            reqs = [dist.P2POp(dist.irecv, staging[offs[k]:offs[k] + sizes[k]], k) for k in range(1, world)]
-        else:
-            reqs = [dist.P2POp(dist.isend, rank_buf[:my_bytes], 0)]
-        for w in dist.batch_isend_irecv(reqs):
-            w.wait()
+        bands.gather_to_rank0(rank_buf, staging, sizes, offs, rank, world)
+        torch.cuda.current_stream().synchronize()      # k_assemble runs on the library's own stream
         if rank == 0:
             r.assemble(W, H, world, staging.data_ptr(), offs, frame.data_ptr())
         e1.record()
