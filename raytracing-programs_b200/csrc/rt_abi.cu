@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <math.h>
+#include <cmath>
 #include <nccl.h>   // types only; symbols come from dlopen("libnccl.so.2")
 #include <stdarg.h>
 #include <stdio.h>
@@ -54,7 +55,8 @@ struct DeviceCtx {
   size_t tile_cap = 0;
   float4 *acc = nullptr, *c0 = nullptr;
   float4 *qbuf = nullptr;     // 6 * tile_cap float4: two queues x {r0,r1,r2}
-  int *qcount = nullptr;      // 16 ints: [0..7] one count per wavefront level (+1 spare), [8..15] work cursors
+  int *qcount = nullptr;      // [8 levels][RT_CTL_STRIDE] queue control words (HitQueue::ctl)
+  int *qcls = nullptr;        // 2 queues x RT_NCLS x tile_cap class lists
   unsigned long long *counters = nullptr;
   // output
   uint8_t *rank_buf = nullptr; size_t rank_cap = 0;
@@ -136,7 +138,7 @@ void free_device(DeviceCtx &d) {
   if (d.dev < 0) return;
   cudaSetDevice(d.dev);
   if (d.stream) cudaStreamSynchronize(d.stream);
-  cudaFree(d.scene_blob); cudaFree(d.acc); cudaFree(d.c0); cudaFree(d.qbuf); cudaFree(d.qcount);
+  cudaFree(d.scene_blob); cudaFree(d.acc); cudaFree(d.c0); cudaFree(d.qbuf); cudaFree(d.qcls); cudaFree(d.qcount);
   cudaFree(d.counters); cudaFree(d.rank_buf); cudaFree(d.staging); cudaFree(d.frame);
   if (d.ev0) cudaEventDestroy(d.ev0);
   if (d.ev1) cudaEventDestroy(d.ev1);
@@ -205,7 +207,7 @@ int rt_init(int n_gpus) {
     d.sm_count = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
-    CK(cudaMalloc((void **)&d.qcount, 16 * sizeof(int)));
+    CK(cudaMalloc((void **)&d.qcount, 8 * RT_CTL_STRIDE * sizeof(int)));
     CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
   }
   g_ndev = n;
@@ -277,7 +279,15 @@ int rt_scene_upload(const rt_scene *scene) {
     lights[4 * l] = make_float4(t.position[0], t.position[1], t.position[2], tyf);
     lights[4 * l + 1] = make_float4(t.color[0], t.color[1], t.color[2], t.cos_theta);
     lights[4 * l + 2] = make_float4(t.radial[0], t.radial[1], t.radial[2], t.a0);
-    lights[4 * l + 3] = make_float4(t.direction[0], t.direction[1], t.direction[2], 0.f);
+    // cull flag: a light behind the surface contributes (0 + 0) * rad * ang (C/raycast.c:414-416),
+    // which is exactly +0 only when rad and ang are certainly finite: radial a0 > 0, a1, a2 >= 0
+    // (denominator >= a0), and for spots an angular exponent evaluated by the integer chain.
+    bool cull_ok = t.radial[0] > 0.0f && t.radial[1] >= 0.0f && t.radial[2] >= 0.0f &&
+                   std::isfinite(t.radial[0]) && std::isfinite(t.radial[1]) && std::isfinite(t.radial[2]);
+    if (t.type == RT_SPOTLIGHT)
+      cull_ok = cull_ok && t.a0 >= 0.0f && t.a0 <= 64.0f && (float)(int)t.a0 == t.a0;
+    if (getenv("RT_NO_CULL")) cull_ok = false;   // debugging aid: trace every shadow ray
+    lights[4 * l + 3] = make_float4(t.direction[0], t.direction[1], t.direction[2], cull_ok ? 1.0f : 0.0f);
   }
   // pad the per-sphere arrays to a multiple of 4 with entries the reject filter never passes
   // (r*r = -inf => k = -inf) so the hot loops can run unrolled without a tail
@@ -379,10 +389,11 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
   size_t tile = tile_pixels_cap();
   if ((long long)tile > px_total) tile = (size_t)(px_total > 0 ? px_total : 1);
   if (tile > d.tile_cap || !d.acc) {
-    cudaFree(d.acc); cudaFree(d.c0); cudaFree(d.qbuf); d.acc = d.c0 = d.qbuf = nullptr; d.tile_cap = 0;
+    cudaFree(d.acc); cudaFree(d.c0); cudaFree(d.qbuf); cudaFree(d.qcls); d.acc = d.c0 = d.qbuf = nullptr; d.qcls = nullptr; d.tile_cap = 0;
     CK(cudaMalloc((void **)&d.acc, tile * sizeof(float4)));
     CK(cudaMalloc((void **)&d.c0, tile * sizeof(float4)));
     CK(cudaMalloc((void **)&d.qbuf, 6 * tile * sizeof(float4)));
+    CK(cudaMalloc((void **)&d.qcls, 2 * RT_NCLS * tile * sizeof(int)));
     d.tile_cap = tile;
   }
   const int lb = pick_lb(d.sc.n_lights);
@@ -403,7 +414,7 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     q[k].r0 = d.qbuf + (size_t)(3 * k) * d.tile_cap;
     q[k].r1 = d.qbuf + (size_t)(3 * k + 1) * d.tile_cap;
     q[k].r2 = d.qbuf + (size_t)(3 * k + 2) * d.tile_cap;
-    q[k].count = nullptr; q[k].cursor = nullptr;
+    q[k].cls = d.qcls + (size_t)k * RT_NCLS * d.tile_cap; q[k].cap = (int)d.tile_cap; q[k].ctl = nullptr;
   }
   CK(cudaMemsetAsync(d.counters, 0, CT_COUNT * sizeof(unsigned long long), d.stream));
   d.evkind.clear();
@@ -414,16 +425,15 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     tg.width = W; tg.height = H; tg.rank = rank; tg.nranks = nranks; tg.band_h = bh;
     tg.first_px = first;
     tg.n_px = (int)((px_total - first) < (long long)tile ? (px_total - first) : (long long)tile);
-    CK(cudaMemsetAsync(d.qcount, 0, 16 * sizeof(int), d.stream));
-    HitQueue q0 = q[0]; q0.count = d.qcount;
+    CK(cudaMemsetAsync(d.qcount, 0, 8 * RT_CTL_STRIDE * sizeof(int), d.stream));
+    HitQueue q0 = q[0]; q0.ctl = d.qcount;
     int gp = (tg.n_px + 256 * RT_PRIM_PX - 1) / (256 * RT_PRIM_PX); if (gp > d.grid_primary) gp = d.grid_primary;
     if ((mr = mark(d, 'p')) != RT_OK) return mr;
-    k_primary<<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, d.counters);
+    k_primary<<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, lb + 1, d.counters);
     plan->launches++;
     for (int level = 0; level < 7; level++) {
       HitQueue qin = q[level & 1], qout = q[(level + 1) & 1];
-      qin.count = d.qcount + level; qout.count = d.qcount + level + 1;
-      qin.cursor = d.qcount + 8 + level; qout.cursor = nullptr;
+      qin.ctl = d.qcount + level * RT_CTL_STRIDE; qout.ctl = d.qcount + (level + 1) * RT_CTL_STRIDE;
       if ((mr = mark(d, 's')) != RT_OK) return mr;
       switch (lb) {
         case 1: launch_shade<1>(d, d.grid_shade, level, qin, qout); break;
@@ -641,7 +651,7 @@ int rt_init_device(int ordinal) {
   d.sm_count = prop.multiProcessorCount;
   CK(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
-  CK(cudaMalloc((void **)&d.qcount, 16 * sizeof(int)));
+  CK(cudaMalloc((void **)&d.qcount, 8 * RT_CTL_STRIDE * sizeof(int)));
   CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
   g_ndev = 1;
   return RT_OK;

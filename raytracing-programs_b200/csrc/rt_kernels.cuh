@@ -35,14 +35,47 @@ RT_DEV bool better_hit(float t, int idx, float best_t, int best_idx) {
   return (t > 0.0f) && (best_t > t || (best_t == t && idx < best_idx && t < RT_INF));
 }
 
-RT_DEV int queue_push_slot(int *count) {
+RT_DEV int warp_agg_add(int *counter) {
   unsigned m = __activemask();
   int lane = threadIdx.x & 31;
   int leader = __ffs(m) - 1;
   int base = 0;
-  if (lane == leader) base = atomicAdd(count, __popc(m));
+  if (lane == leader) base = atomicAdd(counter, __popc(m));
   base = __shfl_sync(m, base, leader);
   return base + __popc(m & ((1u << lane) - 1u));
+}
+
+// Work class of a new hit point: how many ray slots its shading will need (estimate).
+// Same rule as k_shade's ray setup, but on the un-normalised light vector and without
+// caring about rounding: a wrong guess only costs balance, never correctness.
+RT_DEV int hit_class(const DevScene &sc, v3 P, v3 N, int obj, bool can_reflect, int nr_max) {
+  if (nr_max <= 5) return RT_NCLS - 1;   // one scan variant only: nothing to sort
+  const float refl = sc.mat[2 * obj].w, opacity = sc.mat[2 * obj + 1].w;
+  int cnt = (can_reflect && refl > 0.0f) ? 1 : 0;
+  if (opacity > 0.0f) {
+    const int nl = min(sc.n_lights, nr_max - 1);
+    for (int l = 0; l < nl; l++) {
+      const float4 lp = sc.lights[4 * l];
+      const float s = __fmaf_rn(N.z, lp.z - P.z, __fmaf_rn(N.y, lp.y - P.y, N.x * (lp.x - P.x)));
+      cnt += (sc.lights[4 * l + 3].w == 0.0f || !(s <= 0.0f)) ? 1 : 0;
+    }
+  }
+  // classes follow the scan variants of k_shade: <= nr-12, <= nr-8, <= nr-4, <= nr
+  return cnt <= nr_max - 12 ? 0 : cnt <= nr_max - 8 ? 1 : cnt <= nr_max - 4 ? 2 : 3;
+}
+
+RT_DEV void queue_push(const HitQueue &q, float4 a, float4 b, float4 c, int cls) {
+  const int slot = warp_agg_add(&q.ctl[0]);
+  q.r0[slot] = a; q.r1[slot] = b; q.r2[slot] = c;
+  // class list position, aggregated over the lanes that file under the same class so that
+  // neighbouring pixels stay neighbours in the list (their shading shares survivors and cache lines)
+  const unsigned act = __activemask();
+  const unsigned peers = __match_any_sync(act, cls);
+  const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+  int base = 0;
+  if (lane == leader) base = atomicAdd(&q.ctl[1 + cls], __popc(peers));
+  base = __shfl_sync(peers, base, leader);
+  q.cls[(size_t)cls * q.cap + base + __popc(peers & ((1u << lane) - 1u))] = slot;
 }
 
 RT_DEV quad10 load_quad(const float4 *q, int i) {
@@ -80,7 +113,7 @@ RT_DEV void finish_hit(const DevScene &sc, v3 o, v3 d, float t, int idx, v3 &P, 
 #define RT_PRIM_PX 4   // pixels (= primary rays) per thread: one sphere load feeds four reject tests
 __global__ void __launch_bounds__(256)
 k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict__ c0,
-          HitQueue q, unsigned long long *__restrict__ counters) {
+          HitQueue q, int nr_max, unsigned long long *__restrict__ counters) {
   const float pw = __fdiv_rn(sc.cam_w, (float)tg.width);    // C/raycast.c:110
   const float ph = __fdiv_rn(sc.cam_h, (float)tg.height);   // C/raycast.c:109
   const double half_w = __ddiv_rn((double)sc.cam_w, 2.0), half_h = __ddiv_rn((double)sc.cam_h, 2.0);
@@ -176,10 +209,8 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
         n_hits++;
         v3 P, N;
         finish_hit(sc, o, d[k], best_t[k], best_idx[k], P, N);
-        int slot = queue_push_slot(q.count);
-        q.r0[slot] = make_float4(P.x, P.y, P.z, __int_as_float(i));
-        q.r1[slot] = make_float4(N.x, N.y, N.z, __int_as_float(best_idx[k]));
-        q.r2[slot] = make_float4(d[k].x, d[k].y, d[k].z, 1.0f);
+        queue_push(q, make_float4(P.x, P.y, P.z, __int_as_float(i)), make_float4(N.x, N.y, N.z, __int_as_float(best_idx[k])),
+                   make_float4(d[k].x, d[k].y, d[k].z, 1.0f), hit_class(sc, P, N, best_idx[k], true, nr_max));
       }
     }
   }
@@ -209,27 +240,134 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
 // lights.  All slots share origin P and skip index, so per primitive the origin-only
 // part (sphere: tmp, c; plane: num; quadric: c_q) is computed once.
 // ---------------------------------------------------------------------------------
+// Sphere scan of one chunk with NRV ray slots held in registers (loaded from the shared-memory
+// mirror).  Conservative reject filter (DESIGN.md "sphere filter"): with tmp' = P - C,
+// e_j = fma-chain dot(d_j, tmp'), T' = |tmp'|^2, kappa = (T' - r^2) - 2^-18 (T' + r^2):
+//   max_j e_j^2 < kappa  proves the reference's discriminant (C/raycast.c:587) negative for
+//   every ray leaving P, so none of them hits this sphere.
+// Survivors are queued per thread in shared memory (branch-free: the slot is always stored,
+// the queue pointer advances only when the sphere survived) and resolved by the caller, so
+// the scan never diverges.  Four spheres per trip, operands of the next trip in flight; the
+// arrays are padded with entries that never pass (r^2 = -inf => kappa = +inf).
+template <int NRV>
+RT_DEV void scan_chunk(const float (*dsm)[128], unsigned char (*cand)[128], const int tid, const v3 P,
+                       const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
+                       unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
+  const float4 *hp = sc.sph_hot + cs;
+  v3 d[NRV];
+  #pragma unroll
+  for (int j = 0; j < NRV; j++) d[j] = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+  unsigned char *qp = &cand[0][tid];
+  auto scan_pair = [&](const float4 g0, const float4 g1, const int rel) {
+    const float x0 = P.x - g0.x, y0 = P.y - g0.y, z0 = P.z - g0.z;
+    const float x1 = P.x - g1.x, y1 = P.y - g1.y, z1 = P.z - g1.z;
+    const float T0 = __fmaf_rn(z0, z0, __fmaf_rn(y0, y0, x0 * x0));
+    const float T1 = __fmaf_rn(z1, z1, __fmaf_rn(y1, y1, x1 * x1));
+    const float ka0 = __fmaf_rn(-RT_FILTER_EPS, T0 + g0.w, T0 - g0.w);
+    const float ka1 = __fmaf_rn(-RT_FILTER_EPS, T1 + g1.w, T1 - g1.w);
+    float mx0 = 0.0f, mx1 = 0.0f;
+    #pragma unroll
+    for (int j = 0; j < NRV; j++) {
+      mx0 = fmaxf(mx0, fabsf(__fmaf_rn(d[j].z, z0, __fmaf_rn(d[j].y, y0, d[j].x * x0))));
+      mx1 = fmaxf(mx1, fabsf(__fmaf_rn(d[j].z, z1, __fmaf_rn(d[j].y, y1, d[j].x * x1))));
+    }
+    *qp = (unsigned char)rel;
+    qp += (mx0 * mx0 >= ka0) ? 128 : 0;
+    *qp = (unsigned char)(rel + 1);
+    qp += (mx1 * mx1 >= ka1) ? 128 : 0;
+  };
+  float4 a0 = hp[0], a1 = hp[1], b0 = hp[2], b1 = hp[3];
+  #pragma unroll 1
+  for (int s = 0; s < n; s += 4) {
+    hp += 4;
+    const float4 u0 = a0, u1 = a1;
+    a0 = hp[0]; a1 = hp[1];                                  // next trip's operands (4 spare entries at the end)
+    scan_pair(u0, u1, s);
+    const float4 w0 = b0, w1 = b1;
+    b0 = hp[2]; b1 = hp[3];
+    scan_pair(w0, w1, s + 2);
+  }
+  const int nc = (int)(qp - &cand[0][tid]) >> 7;
+  // ---- resolve the survivors of this chunk ---------------------------------------
+  for (int i = 0; i < nc; i++) {
+    const int ss = cs + cand[i][tid];
+    const int idx = sc.sph_idx[ss];
+    if (idx == obj) continue;                                  // C/raycast.c:450
+    const float4 hh = sc.sph_hot[ss];
+    const float xs = P.x - hh.x, ys = P.y - hh.y, zs = P.z - hh.z;
+    const float Ts = __fmaf_rn(zs, zs, __fmaf_rn(ys, ys, xs * xs));
+    const float cp = Ts - hh.w, marg = RT_FILTER_EPS * (Ts + hh.w);
+    const float lo = cp - marg, hi = cp + marg;
+    unsigned pm = 0;                                           // rays the filter does not reject
+    #pragma unroll
+    for (int j = 0; j < NRV; j++) {
+      const float e = __fmaf_rn(d[j].z, zs, __fmaf_rn(d[j].y, ys, d[j].x * xs));
+      pm |= (unsigned)(e * e >= lo) << j;
+    }
+    for (pm &= alive; pm; pm &= pm - 1) {
+      const int j = __ffs(pm) - 1;
+      const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+      const float e = __fmaf_rn(dj.z, zs, __fmaf_rn(dj.y, ys, dj.x * xs));
+      const float e2 = e * e;
+      // Sign analysis: with the discriminant certainly >= 0 (e2 >= hi, or the
+      // origin certainly inside) and c certainly away from 0 relative to e2, the reference's
+      // root selection (C/raycast.c:593-597) yields t > 0 exactly when the origin is inside,
+      // or outside with the sphere ahead (dt < 0).  A shadow ray needs no root then;
+      // whatever is uncertain takes the literal path.
+      const float guard = 1.52587890625e-05f * e2;             // 2^-16 e^2
+      const bool inside = cp <= -(marg + guard);
+      const bool outside = (cp >= marg + guard) && (e2 >= hi);
+      const bool is_refl = r_on && j == 0;
+      const bool need_lit = is_refl ? !(outside && e > 0.0f) : !(inside || outside);
+      bool occl = !is_refl && (inside || (outside && e < 0.0f));
+      if (need_lit) {
+        n_cand++;
+        float t;
+        if (sphere_t_literal(P, dj, sc.sph[ss], t)) {
+          if (is_refl) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
+          else occl = (t > 0.0f) && (t < RT_INF);
+        }
+      }
+      if (occl) alive &= ~(1u << j);
+    }
+  }
+}
+
 template <int LB>
 __global__ void __launch_bounds__(128, RT_SHADE_MINB)
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
         float4 *__restrict__ c0, unsigned long long *__restrict__ counters) {
   constexpr int NR = LB + 1;
+  // ray-slot counts the scan is compiled for; a warp runs the smallest one that holds the
+  // largest number of live rays any of its hit points has
+  constexpr int V3 = NR, V2 = NR > 5 ? NR - 4 : NR, V1 = NR > 9 ? NR - 8 : V2, V0 = NR > 13 ? NR - 12 : V1;
   __shared__ unsigned char cand[RT_CHUNK + 1][128];   // +1: the branch-free push stores before it knows
   __shared__ float dsm[3 * NR][128];
   const int tid = threadIdx.x;
   // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
   // counters are products of these with the scene's primitive counts, formed at the end
   unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_live_sum = 0, n_ls = 0, n_cand = 0;
-  const int n_items = *qin.count;
-  // Dynamic scheduling: every warp claims 32 consecutive queue entries at a time, so no SM
-  // idles while another still holds a backlog of expensive hit points.
+  // Dynamic scheduling: every warp claims 32 consecutive entries of one class list at a time
+  // (heaviest class first), so no SM idles while another still holds a backlog, and the hit
+  // points a warp shades together need about the same number of ray slots.
+  int cstart[RT_NCLS + 1];   // virtual index space: class lists padded to multiples of 32, class 3 first
+  cstart[0] = 0;
+  #pragma unroll
+  for (int c = 0; c < RT_NCLS; c++) cstart[c + 1] = cstart[c] + ((qin.ctl[RT_NCLS - c] + 31) & ~31);
   for (;;) {
-    int item = 0;
-    if ((threadIdx.x & 31) == 0) item = atomicAdd(qin.cursor, 32);
-    item = __shfl_sync(0xffffffffu, item, 0);
-    if (item >= n_items) break;
-    item += threadIdx.x & 31;
-    if (item >= n_items) continue;
+    int vbase = 0;
+    if ((threadIdx.x & 31) == 0) vbase = atomicAdd(&qin.ctl[5], 32);
+    vbase = __shfl_sync(0xffffffffu, vbase, 0);
+    if (vbase >= cstart[RT_NCLS]) break;
+    int c = 0;
+    #pragma unroll
+    for (int k = 1; k < RT_NCLS; k++) c += (vbase >= cstart[k]) ? 1 : 0;
+    const int cls = RT_NCLS - 1 - c;
+    const int k_in = vbase - cstart[c] + (threadIdx.x & 31);
+    const bool have = k_in < qin.ctl[1 + cls];
+    const unsigned vmask = __ballot_sync(0xffffffffu, have);
+    if (!have) continue;
+    const int item = qin.cls[(size_t)cls * qin.cap + k_in];
     const float4 r0 = qin.r0[item], r1 = qin.r1[item], r2 = qin.r2[item];
     const v3 P = mk3(r0.x, r0.y, r0.z), N = mk3(r1.x, r1.y, r1.z), V = mk3(r2.x, r2.y, r2.z);
     const int pix = __float_as_int(r0.w), obj = __float_as_int(r1.w);
@@ -250,115 +388,46 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
 
     const int n_pass = (sc.n_lights + LB - 1) / LB > 0 ? (sc.n_lights + LB - 1) / LB : 1;
     for (int pass = 0; pass < n_pass; pass++) {
-      // ---- ray setup: registers for the sphere scan, a shared-memory copy (dsm) for the
-      // compact run-time-indexed loops (survivors, planes, quadrics, Phong) ----------
+      // ---- ray setup ---------------------------------------------------------------
+      // Slots are packed: the reflection ray (when there is one) takes slot 0, then one slot
+      // per light whose shadow ray can matter.  A light behind the surface (N.L <= 0) gets
+      // no slot: diffuse_light and specular_light both return black for it
+      // (C/raycast.c:714-717, 739-742), so whatever its shadow ray finds, the light adds
+      // exactly +0 to the colour (its attenuations are finite: the host clears the cull flag
+      // of any light for which that is not certain).  The ray still counts as a ray of the
+      // reference semantics (it is cast there, :401); only its work is skipped, like the
+      // rest of a shadow search after its first hit.
+      // Directions go to shared memory (dsm): the sphere scan loads them into registers,
+      // every other section indexes them at run time.
+      const bool r_on = need_refl && pass == 0;
       unsigned alive = 0;
-      {
-        const bool r_on = need_refl && pass == 0;
-        dsm[0][tid] = r_on ? rd.x : 0.f; dsm[1][tid] = r_on ? rd.y : 0.f; dsm[2][tid] = r_on ? rd.z : 0.f;
-        alive = r_on ? 1u : 0u;
-      }
-      #pragma unroll 1
-      for (int j = 1; j < NR; j++) {
-        const int l = pass * LB + j - 1;
-        v3 dj = mk3(0.f, 0.f, 0.f);
-        if (lit && l < sc.n_lights) {
-          const float4 lp = sc.lights[4 * l];
-          dj = norm3(sub3(mk3(lp.x, lp.y, lp.z), P));       // C/raycast.c:396-398
-          alive |= 1u << j;
-        }
-        dsm[3 * j][tid] = dj.x; dsm[3 * j + 1][tid] = dj.y; dsm[3 * j + 2][tid] = dj.z;
-      }
-      v3 d[NR];
-      #pragma unroll
-      for (int j = 0; j < NR; j++) d[j] = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
-      n_live_sum += __popc(alive); n_pass_sum++;
-      // ---- spheres ---------------------------------------------------------------
-      // Scan = conservative reject filter (DESIGN.md "sphere filter").  With tmp' = P - C,
-      // e_j = fma-chain dot(d_j, tmp'), T' = |tmp'|^2, kappa = (T' - r^2) - 2^-18 (T' + r^2):
-      //   max_j e_j^2 < kappa  proves the reference's discriminant (C/raycast.c:587) negative
-      //   for every ray leaving P, so none of them hits this sphere.
-      // Survivors of one chunk of RT_CHUNK spheres are queued per thread in shared memory
-      // and resolved after the chunk, so the scan never diverges.  Two spheres per trip;
-      // the arrays are padded with entries that never pass (r^2 = -inf => kappa = +inf).
-      for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
-        const int ce = min(cs + RT_CHUNK, sc.n_spheres);
-        // The survivor queue is written without a branch: the slot is always stored, the
-        // queue pointer advances only when the sphere survived.
-        unsigned char *qp = &cand[0][tid];
-        auto scan_pair = [&](const float4 g0, const float4 g1, const int rel) {
-          const float x0 = P.x - g0.x, y0 = P.y - g0.y, z0 = P.z - g0.z;
-          const float x1 = P.x - g1.x, y1 = P.y - g1.y, z1 = P.z - g1.z;
-          const float T0 = __fmaf_rn(z0, z0, __fmaf_rn(y0, y0, x0 * x0));
-          const float T1 = __fmaf_rn(z1, z1, __fmaf_rn(y1, y1, x1 * x1));
-          const float ka0 = __fmaf_rn(-RT_FILTER_EPS, T0 + g0.w, T0 - g0.w);
-          const float ka1 = __fmaf_rn(-RT_FILTER_EPS, T1 + g1.w, T1 - g1.w);
-          float mx0 = 0.0f, mx1 = 0.0f;
-          #pragma unroll
-          for (int j = 0; j < NR; j++) {
-            mx0 = fmaxf(mx0, fabsf(__fmaf_rn(d[j].z, z0, __fmaf_rn(d[j].y, y0, d[j].x * x0))));
-            mx1 = fmaxf(mx1, fabsf(__fmaf_rn(d[j].z, z1, __fmaf_rn(d[j].y, y1, d[j].x * x1))));
-          }
-          *qp = (unsigned char)rel;
-          qp += (mx0 * mx0 >= ka0) ? 128 : 0;
-          *qp = (unsigned char)(rel + 1);
-          qp += (mx1 * mx1 >= ka1) ? 128 : 0;
-        };
-        const float4 *hp = sc.sph_hot + cs;
-        float4 a0 = hp[0], a1 = hp[1], b0 = hp[2], b1 = hp[3];
+      unsigned long long lmap = 0;                           // slot -> light of this pass, 4 bits each
+      int cnt = 0;
+      if (r_on) { dsm[0][tid] = rd.x; dsm[1][tid] = rd.y; dsm[2][tid] = rd.z; alive = 1u; cnt = 1; }
+      if (lit) {
         #pragma unroll 1
-        for (int s = cs; s < ce; s += 4) {
-          hp += 4;
-          const float4 u0 = a0, u1 = a1;
-          a0 = hp[0]; a1 = hp[1];                              // next trip's operands (4 spare entries at the end)
-          scan_pair(u0, u1, s - cs);
-          const float4 w0 = b0, w1 = b1;
-          b0 = hp[2]; b1 = hp[3];
-          scan_pair(w0, w1, s - cs + 2);
+        for (int l = pass * LB; l < min(pass * LB + LB, sc.n_lights); l++) {
+          const float4 lp = sc.lights[4 * l];
+          const v3 dj = norm3(sub3(mk3(lp.x, lp.y, lp.z), P));   // C/raycast.c:396-398
+          if (sc.lights[4 * l + 3].w != 0.0f && dot3(N, dj) <= 0.0f) continue;
+          dsm[3 * cnt][tid] = dj.x; dsm[3 * cnt + 1][tid] = dj.y; dsm[3 * cnt + 2][tid] = dj.z;
+          alive |= 1u << cnt;
+          lmap |= (unsigned long long)(l - pass * LB) << (4 * (cnt - (r_on ? 1 : 0)));   // 16 shadow slots x 4 bits
+          cnt++;
         }
-        const int nc = (int)(qp - &cand[0][tid]) >> 7;
-        // ---- resolve the survivors of this chunk ---------------------------------
-        for (int i = 0; i < nc; i++) {
-          const int ss = cs + cand[i][tid];
-          const int idx = sc.sph_idx[ss];
-          if (idx == obj) continue;                            // C/raycast.c:450
-          const float4 hh = sc.sph_hot[ss];
-          const float xs = P.x - hh.x, ys = P.y - hh.y, zs = P.z - hh.z;
-          const float Ts = __fmaf_rn(zs, zs, __fmaf_rn(ys, ys, xs * xs));
-          const float cp = Ts - hh.w, marg = RT_FILTER_EPS * (Ts + hh.w);
-          const float lo = cp - marg, hi = cp + marg;
-          unsigned pm = 0;
-          #pragma unroll
-          for (int j = 0; j < NR; j++) {
-            const float e = __fmaf_rn(d[j].z, zs, __fmaf_rn(d[j].y, ys, d[j].x * xs));
-            pm |= (unsigned)(e * e >= lo) << j;
-          }
-          for (pm &= alive; pm; pm &= pm - 1) {
-            const int j = __ffs(pm) - 1;
-            const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
-            const float e = __fmaf_rn(dj.z, zs, __fmaf_rn(dj.y, ys, dj.x * xs));
-            const float e2 = e * e;
-            // Sign analysis: with the discriminant certainly >= 0 (e2 >= hi, or
-            // the origin certainly inside) and c certainly away from 0 relative to e2, the
-            // reference's root selection (C/raycast.c:593-597) yields t > 0 exactly when the
-            // origin is inside, or outside with the sphere ahead (dt < 0).  A shadow ray
-            // needs no root then; whatever is uncertain takes the literal path.
-            const float guard = 1.52587890625e-05f * e2;       // 2^-16 e^2
-            const bool inside = cp <= -(marg + guard);
-            const bool outside = (cp >= marg + guard) && (e2 >= hi);
-            const bool need_lit = (j == 0) ? !(outside && e > 0.0f) : !(inside || outside);
-            bool occl = (j != 0) && (inside || (outside && e < 0.0f));
-            if (need_lit) {
-              n_cand++;
-              float t;
-              if (sphere_t_literal(P, dj, sc.sph[ss], t)) {
-                if (j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
-                else occl = (t > 0.0f) && (t < RT_INF);
-              }
-            }
-            if (occl) alive &= ~(1u << j);
-          }
-        }
+      }
+      const int wmax = __reduce_max_sync(vmask, cnt);
+      const int nrv = wmax <= V0 ? V0 : wmax <= V1 ? V1 : wmax <= V2 ? V2 : V3;
+      #pragma unroll 1
+      for (int j = cnt; j < nrv; j++) { dsm[3 * j][tid] = 0.f; dsm[3 * j + 1][tid] = 0.f; dsm[3 * j + 2][tid] = 0.f; }
+      n_live_sum += cnt; n_pass_sum++;
+      // ---- spheres ---------------------------------------------------------------
+      for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
+        const int n = min(RT_CHUNK, sc.n_spheres - cs);
+        if (nrv == V0) scan_chunk<V0>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        else if (nrv == V1) scan_chunk<V1>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        else if (nrv == V2) scan_chunk<V2>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        else scan_chunk<V3>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
       }
       // ---- planes ----------------------------------------------------------------
       // t = (-1*num)/den as the reference computes it (C/raycast.c:545-562): den == 0 or
@@ -373,7 +442,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
           const int j = __ffs(m) - 1;
           const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
           const float den = dot3(dj, n);
-          if (j == 0) {
+          if (r_on && j == 0) {
             const float t = __fdiv_rn(nn, den);
             if (den != 0.0f && better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
           } else {
@@ -404,16 +473,16 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
           float t;
           if (quadric_t(P, dj, qq, c_q, t)) {
             if (add32(P.z, mul32(t, dj.z)) < P.z) continue;   // C/raycast.c:492-494 (skip_index != -1 here)
-            if (j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
+            if (r_on && j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
             else if (t > 0.0f && t < RT_INF) alive &= ~(1u << j);
           }
         }
       }
       // ---- Phong for the lights of this pass that stayed unoccluded, in light order
-      for (unsigned m = alive & ~1u; m; m &= m - 1) {
+      for (unsigned m = alive & ~(r_on ? 1u : 0u); m; m &= m - 1) {
         const int j = __ffs(m) - 1;
         n_ls++;
-        const int l = pass * LB + j - 1;
+        const int l = pass * LB + (int)((lmap >> (4 * (j - (r_on ? 1 : 0)))) & 15ull);
         const float4 l0 = sc.lights[4 * l], l1 = sc.lights[4 * l + 1], l2 = sc.lights[4 * l + 2];
         const v3 Lpos = mk3(l0.x, l0.y, l0.z);
         const v3 Ld = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
@@ -459,10 +528,9 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
     if (need_refl && best_idx >= 0) {
       v3 P2, N2;
       finish_hit(sc, P, rd, best_t, best_idx, P2, N2);
-      const int slot = queue_push_slot(qout.count);
-      qout.r0[slot] = make_float4(P2.x, P2.y, P2.z, __int_as_float(pix));
-      qout.r1[slot] = make_float4(N2.x, N2.y, N2.z, __int_as_float(best_idx));
-      qout.r2[slot] = make_float4(rd.x, rd.y, rd.z, mul32(tr, refl));   // total_refl, :345,362
+      queue_push(qout, make_float4(P2.x, P2.y, P2.z, __int_as_float(pix)), make_float4(N2.x, N2.y, N2.z, __int_as_float(best_idx)),
+                 make_float4(rd.x, rd.y, rd.z, mul32(tr, refl)),                  // total_refl, :345,362
+                 hit_class(sc, P2, N2, best_idx, level + 1 < 6, NR));
     }
   }
   unsigned v[7] = {n_refl, n_lit, n_hp, n_pass_sum, n_live_sum, n_ls, n_cand};

@@ -20,17 +20,25 @@ struct DevScene {
   const int *quad_idx;
   const float4 *mat;        // [2*n_shapes] by original index: {Kd.rgb, reflectivity} {Ks.rgb, opacity}
   const int2 *slot;         // [n_shapes] by original index: {type, slot in its type array}
-  const float4 *lights;     // [4*n_lights] {pos, type} {color, cos_theta} {radial a0 a1 a2, angular a0} {dir, 0}
+  const float4 *lights;     // [4*n_lights] {pos, type} {color, cos_theta} {radial a0 a1 a2, angular a0} {dir, cull flag}
 };
 
-// Hit-point queue (one wavefront level): 48 B per entry, structure of float4 arrays.
+// Hit-point queue (one wavefront level): 48 B per entry, structure of float4 arrays, plus one
+// index list per work class.  The producer files every entry under the class of its estimated
+// number of live rays (reflection ray + lights in front of the surface); the consumer walks the
+// lists class by class, so the 32 hit points a warp shades together need about the same number
+// of ray slots.  The class is only a scheduling hint: the consumer sizes its scan from the
+// exact count it computes itself.
+#define RT_NCLS 4
 struct HitQueue {
   float4 *r0;   // P.xyz, pixel (tile-local index, int bits)
   float4 *r1;   // N.xyz, object (original index, int bits)
   float4 *r2;   // V.xyz (direction of the ray that made the hit), throughput
-  int *count;
-  int *cursor;  // work cursor of the launch that consumes this queue (warps claim 32 entries at a time)
+  int *cls;     // [RT_NCLS][cap] entry numbers per class
+  int *ctl;     // [0] entries, [1..RT_NCLS] entries per class, [5] work cursor of the consuming launch
+  int cap;
 };
+#define RT_CTL_STRIDE 8
 
 // Device counters (unsigned long long each).
 enum {
