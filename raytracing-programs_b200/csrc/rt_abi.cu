@@ -229,7 +229,7 @@ int rt_scene_upload(const rt_scene *scene) {
       (scene->num_shapes > 0 && !scene->shapes) || (scene->num_lights > 0 && !scene->lights))
     return set_err(RT_ERR_ARG, "bad scene argument");
   const int n = scene->num_shapes, nl = scene->num_lights;
-  std::vector<float4> sph, sph_hot, sph_prim, pln, quad, mat(2 * (size_t)n + 1), lights(4 * (size_t)nl + 1);
+  std::vector<float4> sph, sph_hot, sph_prim, pln, quad, quad_hot, quad_prim, mat(2 * (size_t)n + 1), lights(4 * (size_t)nl + 1);
   std::vector<int> sph_idx, pln_idx, quad_idx;
   std::vector<int2> slot((size_t)n + 1);
   for (int i = 0; i < n; i++) {
@@ -266,6 +266,18 @@ int rt_scene_upload(const rt_scene *scene) {
       quad.push_back(make_float4(s.params[0], s.params[1], s.params[2], s.params[3]));
       quad.push_back(make_float4(s.params[4], s.params[5], s.params[6], s.params[7]));
       quad.push_back(make_float4(s.params[8], s.params[9], 0.f, 0.f));
+      {
+        const float *q = s.params;
+        const float S2 = fabsf(q[0]) + fabsf(q[1]) + fabsf(q[2]) + fabsf(q[3]) + fabsf(q[4]) + fabsf(q[5]);
+        const float S1 = fabsf(q[6]) + fabsf(q[7]) + fabsf(q[8]);
+        const float4 h0 = make_float4(q[0], q[1], q[2], q[3]), h1 = make_float4(q[4], q[5], q[6], q[7]),
+                     h2 = make_float4(q[8], q[9], S2 * 1.000001f, S1 * 1.000001f);
+        quad_hot.push_back(h0); quad_hot.push_back(h1); quad_hot.push_back(h2);
+        const QuadFilter f = quad_filter_setup(h0, h1, h2, 0.0f, 0.0f, 0.0f);
+        quad_prim.push_back(make_float4(f.As, f.Bs, f.Cs, f.Ds));
+        quad_prim.push_back(make_float4(f.Es, f.Fs, f.m0, f.eb));
+        quad_prim.push_back(make_float4(f.gx, f.gy, f.gz, 0.f));
+      }
       quad_idx.push_back(i);
     } else {
       return set_err(RT_ERR_ARG, "shape %d has unknown type %d", i, s.type);
@@ -291,6 +303,7 @@ int rt_scene_upload(const rt_scene *scene) {
   }
   // pad the per-sphere arrays to a multiple of 4 with entries the reject filter never passes
   // (r*r = -inf => k = -inf) so the hot loops can run unrolled without a tail
+  for (int k = 0; k < 3; k++) quad_hot.push_back(make_float4(0.f, 0.f, 0.f, 0.f));   // prefetch spare
   const size_t padded = (sph_hot.size() + 3) / 4 * 4 + 4;   // + one prefetch group
   while (sph_hot.size() < padded) {
     sph_hot.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));
@@ -301,13 +314,14 @@ int rt_scene_upload(const rt_scene *scene) {
   const int n_sph_real = (int)slot_count_spheres;
   // one blob, 256-byte aligned sections
   struct Sec { const void *src; size_t bytes; size_t off; };
-  Sec secs[11] = {
+  Sec secs[13] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
       {quad_idx.data(), quad_idx.size() * 4, 0}, {mat.data(), mat.size() * 16, 0},
       {slot.data(), slot.size() * 8, 0},       {lights.data(), lights.size() * 16, 0},
-      {sph_hot.data(), sph_hot.size() * 16, 0}};
+      {sph_hot.data(), sph_hot.size() * 16, 0}, {quad_hot.data(), quad_hot.size() * 16, 0},
+      {quad_prim.data(), quad_prim.size() * 16, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -333,6 +347,7 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.quad_idx = (const int *)(b + secs[6].off); sc.mat = (const float4 *)(b + secs[7].off);
     sc.slot = (const int2 *)(b + secs[8].off); sc.lights = (const float4 *)(b + secs[9].off);
     sc.sph_hot = (const float4 *)(b + secs[10].off);
+    sc.quad_hot = (const float4 *)(b + secs[11].off); sc.quad_prim = (const float4 *)(b + secs[12].off);
   }
   g_have_scene = true;
   g_n_lights = nl;

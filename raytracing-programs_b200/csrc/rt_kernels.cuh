@@ -15,6 +15,7 @@
 #endif
 #define RT_CHUNK 128     /* spheres per scan chunk = capacity of the per-thread survivor queue */
 #define RT_INF __int_as_float(0x7f800000)
+#define RT_NAN __int_as_float(0x7fc00000)
 #define RT_FILTER_EPS 3.814697265625e-06f   /* 2^-18, margin of the sphere reject filter */
 
 struct TileGeom {
@@ -187,14 +188,29 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
       }
     }
     n_pln += (unsigned long long)sc.n_planes * n_live;
+    // quadrics: the origin is (0,0,0), so the filter's origin-only part is a per-quadric
+    // constant prepared on the host (quad_prim); survivors take the reference's expression tree
     for (int kq = 0; kq < sc.n_quadrics; kq++) {
-      quad10 qq = load_quad(sc.quad, kq);
-      float c_q = (float)quadric_cq(o, qq);
-      int idx = sc.quad_idx[kq];
-      #pragma unroll 1
-      for (int k = 0; k < RT_PRIM_PX; k++) {
-        float t;   // skip_index == -1: no z rule on primary rays
-        if (((live >> k) & 1u) && quadric_t(o, d[k], qq, c_q, t) && better_hit(t, idx, best_t[k], best_idx[k])) { best_t[k] = t; best_idx[k] = idx; }
+      const float4 p0 = sc.quad_prim[3 * kq], p1 = sc.quad_prim[3 * kq + 1], p2 = sc.quad_prim[3 * kq + 2];
+      QuadFilter f;
+      f.As = p0.x; f.Bs = p0.y; f.Cs = p0.z; f.Ds = p0.w; f.Es = p1.x; f.Fs = p1.y; f.m0 = p1.z; f.eb = p1.w;
+      f.gx = p2.x; f.gy = p2.y; f.gz = p2.z;
+      float v[RT_PRIM_PX];
+      float vmax = -1.0f;
+      #pragma unroll
+      for (int k = 0; k < RT_PRIM_PX; k++) { v[k] = quad_filter_v(f, d[k]); vmax = fmaxf(vmax, v[k]); }
+      if (vmax >= 0.0f) {
+        const quad10 qq = load_quad(sc.quad, kq);
+        const float c_q = (float)quadric_cq(o, qq);
+        const int idx = sc.quad_idx[kq];
+        #pragma unroll 1
+        for (int k = 0; k < RT_PRIM_PX; k++) {
+          float t;   // skip_index == -1: no z rule on primary rays
+          if (v[k] >= 0.0f && ((live >> k) & 1u)) {
+            n_cand++;
+            if (quadric_t(o, d[k], qq, c_q, t) && better_hit(t, idx, best_t[k], best_idx[k])) { best_t[k] = t; best_idx[k] = idx; }
+          }
+        }
       }
     }
     n_quad += (unsigned long long)sc.n_quadrics * n_live;
@@ -333,6 +349,58 @@ RT_DEV void scan_chunk(const float (*dsm)[128], unsigned char (*cand)[128], cons
   }
 }
 
+// Quadric scan of one chunk, same structure as scan_chunk: conservative FP32 reject filter
+// (rt_math.cuh, "quadric filter") for NRV rays in registers, survivors queued per thread and
+// resolved by the reference's expression tree (quadric_cq / quadric_t, mixed float/double)
+// plus the z rule of C/raycast.c:492-494.
+template <int NRV>
+RT_DEV void scan_quadrics(const float (*dsm)[128], unsigned char (*cand)[128], const int tid, const v3 P,
+                          const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
+                          unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
+  v3 d[NRV];
+  #pragma unroll
+  for (int j = 0; j < NRV; j++) d[j] = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+  unsigned char *qp = &cand[0][tid];
+  const float4 *hp = sc.quad_hot + 3 * (size_t)cs;
+  float4 a0 = hp[0], a1 = hp[1], a2 = hp[2];
+  #pragma unroll 1
+  for (int k = 0; k < n; k++) {
+    hp += 3;
+    const QuadFilter f = quad_filter_setup(a0, a1, a2, P.x, P.y, P.z);
+    a0 = hp[0]; a1 = hp[1]; a2 = hp[2];                      // next quadric (one spare entry at the end)
+    float vmax = -1.0f;
+    #pragma unroll
+    for (int j = 0; j < NRV; j++) vmax = fmaxf(vmax, quad_filter_v(f, d[j]));
+    *qp = (unsigned char)k;
+    qp += (vmax >= 0.0f) ? 128 : 0;
+  }
+  const int nc = (int)(qp - &cand[0][tid]) >> 7;
+  for (int i = 0; i < nc; i++) {
+    const int kk = cs + cand[i][tid];
+    const int idx = sc.quad_idx[kk];
+    if (idx == obj) continue;                                  // C/raycast.c:450
+    const QuadFilter f = quad_filter_setup(sc.quad_hot[3 * kk], sc.quad_hot[3 * kk + 1], sc.quad_hot[3 * kk + 2], P.x, P.y, P.z);
+    unsigned pm = 0;
+    #pragma unroll
+    for (int j = 0; j < NRV; j++) pm |= (unsigned)(quad_filter_v(f, d[j]) >= 0.0f) << j;
+    pm &= alive;
+    if (!pm) continue;
+    const quad10 qq = load_quad(sc.quad, kk);
+    const float c_q = (float)quadric_cq(P, qq);
+    for (; pm; pm &= pm - 1) {
+      const int j = __ffs(pm) - 1;
+      const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+      float t;
+      n_cand++;
+      if (quadric_t(P, dj, qq, c_q, t)) {
+        if (add32(P.z, mul32(t, dj.z)) < P.z) continue;       // C/raycast.c:492-494 (skip_index != -1 here)
+        if (r_on && j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
+        else if (t > 0.0f && t < RT_INF) alive &= ~(1u << j);
+      }
+    }
+  }
+}
+
 template <int LB>
 __global__ void __launch_bounds__(128, RT_SHADE_MINB)
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
@@ -419,7 +487,8 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
       const int wmax = __reduce_max_sync(vmask, cnt);
       const int nrv = wmax <= V0 ? V0 : wmax <= V1 ? V1 : wmax <= V2 ? V2 : V3;
       #pragma unroll 1
-      for (int j = cnt; j < nrv; j++) { dsm[3 * j][tid] = 0.f; dsm[3 * j + 1][tid] = 0.f; dsm[3 * j + 2][tid] = 0.f; }
+      // unused slots of the chosen scan variant hold NaN: they lose every max and pass no test
+      for (int j = cnt; j < nrv; j++) { dsm[3 * j][tid] = RT_NAN; dsm[3 * j + 1][tid] = RT_NAN; dsm[3 * j + 2][tid] = RT_NAN; }
       n_live_sum += cnt; n_pass_sum++;
       // ---- spheres ---------------------------------------------------------------
       for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
@@ -462,21 +531,12 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
         }
       }
       // ---- quadrics --------------------------------------------------------------
-      for (int k = 0; k < sc.n_quadrics; k++) {
-        const int idx = sc.quad_idx[k];
-        if (idx == obj) continue;
-        const quad10 qq = load_quad(sc.quad, k);
-        const float c_q = (float)quadric_cq(P, qq);
-        for (unsigned m = alive; m; m &= m - 1) {
-          const int j = __ffs(m) - 1;
-          const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
-          float t;
-          if (quadric_t(P, dj, qq, c_q, t)) {
-            if (add32(P.z, mul32(t, dj.z)) < P.z) continue;   // C/raycast.c:492-494 (skip_index != -1 here)
-            if (r_on && j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
-            else if (t > 0.0f && t < RT_INF) alive &= ~(1u << j);
-          }
-        }
+      for (int cs = 0; cs < sc.n_quadrics; cs += RT_CHUNK) {
+        const int n = min(RT_CHUNK, sc.n_quadrics - cs);
+        if (nrv == V0) scan_quadrics<V0>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        else if (nrv == V1) scan_quadrics<V1>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        else if (nrv == V2) scan_quadrics<V2>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        else scan_quadrics<V3>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
       }
       // ---- Phong for the lights of this pass that stayed unoccluded, in light order
       for (unsigned m = alive & ~(r_on ? 1u : 0u); m; m &= m - 1) {

@@ -143,3 +143,53 @@ RT_DEV bool quadric_t(v3 o, v3 d, const quad10 &q, float c_q, float &t) {
   if (t <= 0.0f) t = (float)__ddiv_rn(add64(nb, sq), den);
   return true;
 }
+
+// ---- conservative FP32 reject filter for quadrics (DESIGN.md "quadric filter") -------
+// The reference (C/raycast.c:614-656) misses a quadric when a_q != 0 and
+// disc = b_q^2 - 4 a_q c_q < 0.  With FP32/FMA estimates a', b', c' of the three
+// coefficients and bounds on what separates them from the reference's floats
+//   |a_q - a'| <= ea = 2^-19 S2,   |b_q - b'| <= eb = 2^-19 (2 S2 om + S1),
+//   |c_q - c'| <= ec = 2^-19 (S2 om^2 + S1 om + |J|)
+// (S2 = |A|+..+|F|, S1 = |G|+|H|+|I|, om = max |origin component|, |d| = 1; the true
+// separations are below 12 u times the same sums), a ray certainly misses when
+//   (|b'| + eb)^2  <  4 (|c'| - ec)(1 - 2^-18) (sigma a' - ea),   sigma = sign(c'),
+// because then sign(a_q) = sign(c_q), a_q != 0 and b_q^2 < 4 a_q c_q with a relative gap of
+// 2^-18.  Everything that depends only on the origin is folded into scaled coefficients,
+// so one ray costs 9 + 3 + 2 FMA-pipe instructions:  v = beta^2 - m,  v < 0  =>  miss.
+#define RT_QUAD_EPS 1.9073486328125e-06f   /* 2^-19 */
+struct QuadFilter {
+  float As, Bs, Cs, Ds, Es, Fs, m0;   // K4 sigma * (A..F), -K4 ea
+  float gx, gy, gz, eb;               // gradient estimate at the origin, bound on b
+};
+// q0 = {A,B,C,D}, q1 = {E,F,G,H}, q2 = {I,J,S2,S1}
+__host__ __device__ inline QuadFilter quad_filter_setup(float4 q0, float4 q1, float4 q2, float ox, float oy, float oz) {
+  const float A = q0.x, B = q0.y, C = q0.z, D = q0.w, E = q1.x, F = q1.y, G = q1.z, H = q1.w, I = q2.x, J = q2.y;
+  const float S2 = q2.z, S1 = q2.w;
+  const float om = fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz)));
+  QuadFilter f;
+  f.gx = fmaf(2.0f * A, ox, fmaf(D, oy, fmaf(E, oz, G)));
+  f.gy = fmaf(D, ox, fmaf(2.0f * B, oy, fmaf(F, oz, H)));
+  f.gz = fmaf(E, ox, fmaf(F, oy, fmaf(2.0f * C, oz, I)));
+  const float u1 = fmaf(A, ox, fmaf(D, oy, fmaf(E, oz, G))), u2 = fmaf(B, oy, fmaf(F, oz, H)), u3 = fmaf(C, oz, I);
+  const float cp = fmaf(ox, u1, fmaf(oy, u2, fmaf(oz, u3, J)));
+  const float cabs = fmaf(S2, om * om, fmaf(S1, om, fabsf(J)));
+  f.eb = RT_QUAD_EPS * fmaf(2.0f * S2, om, S1);
+  const float C1 = fabsf(cp) - RT_QUAD_EPS * cabs;
+  // K4 = 0 switches the filter off for this quadric and origin (everything survives):
+  // c too close to 0 to know its sign, or magnitudes where the scaled products could overflow.
+  float K4 = 0.0f;
+  if (C1 > 0.0f && C1 < 1e15f && S2 < 1e15f) K4 = copysignf(4.0f * C1 * (1.0f - 3.814697265625e-06f), cp);
+  f.As = K4 * A; f.Bs = K4 * B; f.Cs = K4 * C; f.Ds = K4 * D; f.Es = K4 * E; f.Fs = K4 * F;
+  f.m0 = -fabsf(K4) * (RT_QUAD_EPS * 1.0001f * S2);
+  return f;
+}
+// v >= 0 (or NaN-free inputs that cannot be rejected) => the ray survives the filter.
+RT_DEV float quad_filter_v(const QuadFilter &f, v3 d) {
+  const float u1 = __fmaf_rn(f.Es, d.z, __fmaf_rn(f.Ds, d.y, f.As * d.x));
+  const float u2 = __fmaf_rn(f.Fs, d.z, f.Bs * d.y);
+  const float u3 = f.Cs * d.z;
+  const float m = __fmaf_rn(d.x, u1, __fmaf_rn(d.y, u2, __fmaf_rn(u3, d.z, f.m0)));
+  const float b = __fmaf_rn(f.gz, d.z, __fmaf_rn(f.gy, d.y, f.gx * d.x));
+  const float beta = fabsf(b) + f.eb;
+  return __fmaf_rn(beta, beta, -m);
+}

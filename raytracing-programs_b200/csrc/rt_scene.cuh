@@ -17,6 +17,8 @@ struct DevScene {
   const float4 *pln;        // [2*n_planes] {px,py,pz,0} {nx,ny,nz,0}
   const int *pln_idx;
   const float4 *quad;       // [3*n_quadrics] {a,b,c,d} {e,f,g,h} {i,j,0,0}
+  const float4 *quad_hot;   // [3*(n_quadrics+1)] reject-filter operands {A,B,C,D} {E,F,G,H} {I,J,S2,S1}
+  const float4 *quad_prim;  // [3*n_quadrics] filter constants for the origin (0,0,0): {As,Bs,Cs,Ds} {Es,Fs,m0,eb} {gx,gy,gz,0}
   const int *quad_idx;
   const float4 *mat;        // [2*n_shapes] by original index: {Kd.rgb, reflectivity} {Ks.rgb, opacity}
   const int2 *slot;         // [n_shapes] by original index: {type, slot in its type array}
