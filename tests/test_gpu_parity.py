@@ -156,3 +156,26 @@ def test_errors_are_loud(renderer):
     lib = renderer.lib
     assert lib.rt_render(0, 10, None, None) != 0
     assert lib.rt_last_error()
+
+
+ZOO = ["zoo_quadrics", "zoo_spheres", "zoo_lights", "zoo_far"]
+
+
+@pytest.mark.parametrize("name", ZOO)
+def test_zoo_scenes(renderer, name):
+    """Adversarial scenes for the conservative filters (tests/golden/make_zoo.py): every quadric
+    family incl. the a_q == 0 path, touching/nested spheres, lights inside spheres and on surfaces,
+    spot lights, never-culled lights, two light passes, content far from the origin."""
+    path = os.path.join(rtlib.SCENES, f"{name}.scene")
+    gold = np.load(os.path.join(rtlib.GOLDEN, "zoo.npz"))[name]
+    renderer.upload(path)
+    img, st = renderer.raycast(gold.shape[1], gold.shape[0])
+    rep = rtlib.compare(img, gold)
+    print(name, rep, st.as_dict())
+    assert rep["identical_frac"] == 1.0, rep
+    for W, H in ((257, 131), (640, 480)):
+        img, st = renderer.raycast(W, H)
+        ora, ct = rtlib.oracle_render(path, W, H, counters=True)
+        rep = rtlib.compare(img, ora)
+        assert rep["identical_frac"] == 1.0, (W, H, rep)
+        assert int(st.rays_shadow) == ct.rays_shadow and int(st.rays_reflection) == ct.rays_reflection

@@ -99,3 +99,15 @@ def test_rows_are_independent():
     full = rtlib.oracle_render(scene_path("reflection"), 96, 64)
     some = rtlib.oracle_render(scene_path("reflection"), 96, 64, rows=[63, 0, 31])
     assert (some == full[[63, 0, 31]]).all()
+
+
+ZOO = ["zoo_quadrics", "zoo_spheres", "zoo_lights", "zoo_far"]
+
+
+@pytest.mark.parametrize("name", ZOO)
+def test_oracle_matches_golden_zoo(name):
+    """Adversarial scenes (tests/golden/make_zoo.py): restatement vs the reference's own render."""
+    gold = np.load(os.path.join(rtlib.GOLDEN, "zoo.npz"))[name]
+    img = rtlib.oracle_render(os.path.join(rtlib.SCENES, f"{name}.scene"), gold.shape[1], gold.shape[0])
+    rep = rtlib.compare(img, gold)
+    assert rep["identical_frac"] == 1.0, rep
