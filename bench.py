@@ -142,6 +142,60 @@ def run_reference_arm(args, name, scene_path, W, H):
         "gpu_launches": 0}))
 
 
+def p3_leg(r, W, H, frame, flush, pk, host_frame, cpu=True):
+    """ppm_WriteOutP3 on the GPU (k_p3_format): device-to-device GB/s against the measured HBM copy
+    peak, the host-facing writer end to end, and the reference's fprintf loop on a sample."""
+    import torch
+    lib = pkg.load_library()
+    cap = lib.rt_p3_max_bytes(W, H)
+    text = torch.empty(cap + 64, dtype=torch.uint8, device=frame.device)
+    ms = []
+    nbytes = 0
+    for i in range(7):                                   # 2 warm-up + 5 timed, L2 flushed in between
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        nbytes, st = r.p3_format_device(frame.data_ptr(), W, H, text.data_ptr(), cap)
+        if i >= 2:
+            ms.append(st.ms_format)
+    m = statistics.median(ms)
+    n_values = W * H * 3
+    alg = n_values + nbytes                              # 1 byte read per value + the text written
+    got = bytes(text[:64].cpu().numpy())
+    # end to end: the frame the last rt_render left on GPU 0 -> text in host memory (pinned slabs), sink discards
+    total = [0]
+
+    def sink(_data, n, _user):
+        total[0] += n
+        return 0
+    cb = pkg.P3_SINK(sink)
+    st2 = pkg.RtP3Stats()
+    e2e_ms = None
+    t0 = time.perf_counter()
+    rc = lib.rt_p3_write(None, W, H, 255, cb, None, C.byref(st2))
+    if rc == 0:
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+    leg = {"kernel": "k_p3_format", "text_bytes": int(nbytes), "values": n_values, "ms_format": m,
+           "gvalues_per_s": n_values / m / 1e6,
+           "roofline": {"bound": "hbm", "achieved": alg / m / 1e6, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                        "frac": alg / m / 1e6 / pk["hbm_gbs"], "traffic": None,
+                        "algorithmic_bytes_per_value": alg / n_values},
+           "head": got[:24].decode(errors="replace"),
+           "e2e_resident_frame_to_host_text_ms": e2e_ms, "e2e_text_bytes": total[0]}
+    if cpu:
+        import rtlib
+        if rtlib.ref_available():
+            rows = min(H, max(1, (8 << 20) // W))        # ~8 Mpixel sample: ~2 s of fprintf
+            ref = rtlib.ref()
+            ref.ref_write_p3.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+            sample = host_frame.numpy()[:rows * W * 3]
+            t0 = time.perf_counter()
+            ref.ref_write_p3(b"/dev/null", W, rows, 255, sample.ctypes.data_as(C.c_void_p))
+            dt = time.perf_counter() - t0
+            leg["cpu_baseline"] = {"value": rows * W * 3 / dt / 1e9, "unit": "Gvalues/s", "cores": 1, "kind": "reference",
+                                   "sample": f"ppm_WriteOutP3 of the first {rows} rows to /dev/null, {dt:.2f} s"}
+    return leg
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -332,6 +386,9 @@ def main():
                          "pixels": rep["pixels"], "identical_frac": rep["identical_frac"], "max_abs_diff": rep["max_abs_diff"],
                          "divergent_pixels": rep["pixels"] - rep["identical"]}
 
+    # ---- P3 writer: HBM-bound formatter on the same frame -------
+    if world == 1 and not args.no_extra:
+        out["p3_writer"] = p3_leg(r, W, H, frame, flush, pk, host_frame, cpu=not args.no_cpu)
     # ---- the small shipped configs, for the record (N = 1 only) --------------------------
     if world == 1 and not args.no_extra and not args.size:
         extra = {}

@@ -150,6 +150,36 @@ int64_t rt_rank_num_rows(int height, int rank, int nranks);
 /* Fills rows_out[0..n) with the image row of each row of the rank buffer; returns n. */
 int64_t rt_rank_rows(int height, int rank, int nranks, int32_t *rows_out);
 
+/* ---- P3 writer -------------------------------------------
+ * The body of ppm_WriteOutP3 (C/ppm.c:168-184) formatted on the GPU: header
+ * "P3\n<w> <h> \n<maxColor>\n" (the space before the second newline is the reference's),
+ * then every byte of the pixmap as "%d\n", in pixmap order.  Byte-identical to the
+ * reference's file for any pixmap; sizes in size_t (the reference's int indexing
+ * overflows above ~26.7k^2). */
+typedef struct rt_p3_stats {
+  uint64_t text_bytes;          /* header + body */
+  double ms_h2d;                /* upload of host_rgb (0 when the resident frame is used) */
+  double ms_format;             /* k_p3_format, CUDA events on the launching stream */
+  double ms_total;              /* whole call, host clock (includes the sink) */
+} rt_p3_stats;
+
+/* Upper bound of the text of a W x H frame: header + 4 bytes per value. */
+size_t rt_p3_max_bytes(int width, int height);
+
+/* Device to device: dev_rgb (3*W*H bytes, 16-byte aligned) -> dev_text (16-byte aligned,
+ * capacity text_cap >= rt_p3_max_bytes); *text_bytes receives the exact length. */
+int rt_p3_format_device(const void *dev_rgb, int width, int height, unsigned max_color,
+                        void *dev_text, size_t text_cap, size_t *text_bytes, rt_p3_stats *stats);
+
+/* Consumer of the text, called with consecutive pieces in order; non-zero aborts. */
+typedef int (*rt_p3_sink)(const void *data, size_t nbytes, void *user);
+
+/* Host-facing writer: formats host_rgb (uploaded first) or, when host_rgb is NULL, the
+ * frame the last rt_render / rt_render_device left on GPU 0 (its size must be W x H), and
+ * streams the text through pinned double buffers to the sink (e.g. an fwrite). */
+int rt_p3_write(const uint8_t *host_rgb, int width, int height, unsigned max_color,
+                rt_p3_sink sink, void *user, rt_p3_stats *stats);
+
 #ifdef __cplusplus
 }
 #endif

@@ -156,3 +156,17 @@ int ref_isect_quadric(const float *o, const float *d, const float *q10, float *t
   float *u = &s.a; for (int k = 0; k < 10; k++) u[k] = q10[k];
   return ray_intersect_quadric((float *)o, (float *)d, &s, t);
 }
+
+/* The reference's own P3 writer (C/ppm.c:168-184, linked from the reference's ppm.c) on a
+ * caller-supplied pixmap: pins the P3 restatement and the GPU formatter. 0 = ok. */
+int ref_write_p3(const char *path, int width, int height, int max_color, uint8_t *pixmap) {
+  FILE *f = fopen(path, "wb");
+  if (!f) return -1;
+  PPMFormat p;
+  memset(&p, 0, sizeof p);
+  p.width = width; p.height = height; p.size = width * height * 3;
+  p.maxColor = (uint8_t)max_color; p.depth = 3; p.pixmap = pixmap;
+  ppm_WriteOutP3(p, f);
+  fclose(f);
+  return 0;
+}

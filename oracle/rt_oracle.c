@@ -319,3 +319,23 @@ int orc_isect_quadric(const float *o, const float *d, const float *q10, float *t
   for (int k = 0; k < 10; k++) s.params[k] = q10[k];
   return isect_quadric(o, d, &s, t);
 }
+
+/* ---- P3 writer restatement (C/ppm.c:168-184): "P3\n", "%d %d \n%u\n", then per pixel
+ * "%d\n%d\n%d\n" of the three channel bytes, rows top to bottom.  Writes into out (capacity
+ * cap) and returns the length, or 0 when cap is too small.  size_t indexing (the reference's
+ * int arithmetic is the same below 2^31 values). */
+#include <stdio.h>
+size_t orc_p3_format(const uint8_t *pixmap, int width, int height, unsigned max_color, char *out, size_t cap) {
+  size_t n = 0;
+  if (cap < 64) return 0;
+  n += (size_t)sprintf(out + n, "P3\n");
+  n += (size_t)sprintf(out + n, "%d %d \n%u\n", width, height, (unsigned)(uint8_t)max_color);
+  for (int y = 0; y < height; y++) {
+    for (int x = 0; x < width; x++) {
+      const uint8_t *pixel = &pixmap[3 * ((size_t)y * (size_t)width + (size_t)x)];
+      if (n + 16 > cap) return 0;
+      n += (size_t)sprintf(out + n, "%d\n%d\n%d\n", pixel[0], pixel[1], pixel[2]);
+    }
+  }
+  return n;
+}

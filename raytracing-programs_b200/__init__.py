@@ -52,9 +52,16 @@ class RtStats(C.Structure):
         return self.rays_primary + self.rays_reflection + self.rays_shadow
 
 
+class RtP3Stats(C.Structure):
+    _fields_ = [("text_bytes", C.c_uint64), ("ms_h2d", C.c_double), ("ms_format", C.c_double), ("ms_total", C.c_double)]
+
+
+P3_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p)
+
 ABI_SYMBOLS = ("rt_init", "rt_init_device", "rt_device_count", "rt_shutdown", "rt_last_error",
                "rt_abi_version", "rt_scene_upload", "rt_render", "rt_render_device", "rt_render_rank",
-               "rt_assemble_device", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows")
+               "rt_assemble_device", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows",
+               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write")
 
 _lib = None
 _host = None
@@ -82,6 +89,11 @@ def load_library():
     lib.rt_rank_num_rows.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.rt_rank_rows.restype = C.c_int64
     lib.rt_rank_rows.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int32)]
+    lib.rt_p3_max_bytes.restype = C.c_size_t
+    lib.rt_p3_max_bytes.argtypes = [C.c_int, C.c_int]
+    lib.rt_p3_format_device.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_size_t,
+                                        C.POINTER(C.c_size_t), C.POINTER(RtP3Stats)]
+    lib.rt_p3_write.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, P3_SINK, C.c_void_p, C.POINTER(RtP3Stats)]
     _lib = lib
     return lib
 
@@ -167,6 +179,33 @@ class Renderer:
         arr = (C.c_int64 * len(offsets))(*offsets)
         _check(self.lib, self.lib.rt_assemble_device(width, height, nranks, C.c_void_p(staging_ptr), arr,
                                                      C.c_void_p(frame_ptr)), "rt_assemble_device")
+
+    def p3_text(self, width, height, pixmap=None, max_color=255):
+        """ppm_WriteOutP3 (C/ppm.c:168-184) on the GPU: the P3 file of `pixmap` (numpy uint8
+        [H, W, 3]) or, when None, of the frame the last render left on GPU 0.  Returns (bytes, RtP3Stats)."""
+        pieces = []
+
+        def sink(data, n, _user):
+            pieces.append(C.string_at(data, n))
+            return 0
+        cb = P3_SINK(sink)
+        st = RtP3Stats()
+        ptr = None
+        if pixmap is not None:
+            import numpy as np
+            pixmap = np.ascontiguousarray(pixmap, dtype=np.uint8)
+            assert pixmap.size == width * height * 3
+            ptr = pixmap.ctypes.data_as(C.c_void_p)
+        _check(self.lib, self.lib.rt_p3_write(ptr, width, height, max_color, cb, None, C.byref(st)), "rt_p3_write")
+        return b"".join(pieces), st
+
+    def p3_format_device(self, rgb_ptr, width, height, text_ptr, text_cap, max_color=255):
+        """Device to device; returns (text length, RtP3Stats)."""
+        st = RtP3Stats()
+        n = C.c_size_t()
+        _check(self.lib, self.lib.rt_p3_format_device(C.c_void_p(rgb_ptr), width, height, max_color, C.c_void_p(text_ptr),
+                                                      text_cap, C.byref(n), C.byref(st)), "rt_p3_format_device")
+        return n.value, st
 
     def close(self):
         self.lib.rt_shutdown()

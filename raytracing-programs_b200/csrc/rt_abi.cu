@@ -16,6 +16,7 @@
 
 #include "rt_abi.h"
 #include "rt_kernels.cuh"
+#include "rt_p3.cuh"
 
 #define RT_MAX_GPUS 8
 
@@ -66,6 +67,12 @@ struct DeviceCtx {
   // one event before every launch (+1 at the end): per-kernel-class device times
   std::vector<cudaEvent_t> evpool;
   std::vector<char> evkind;   // 'p' primary, 's' shade, 'f' finalize
+  // P3 writer (device 0 only)
+  char *p3_text = nullptr; size_t p3_text_cap = 0;
+  unsigned long long *p3_state = nullptr; size_t p3_state_cap = 0;   // span offsets + span lengths (bytes)
+  char *p3_pinned[2] = {nullptr, nullptr}; size_t p3_pinned_cap = 0;
+  cudaEvent_t p3_ev[2] = {nullptr, nullptr};
+  int frame_w = 0, frame_h = 0;   // size of the frame currently held in `frame`
 };
 
 DeviceCtx g_dev[RT_MAX_GPUS];
@@ -140,6 +147,8 @@ void free_device(DeviceCtx &d) {
   if (d.stream) cudaStreamSynchronize(d.stream);
   cudaFree(d.scene_blob); cudaFree(d.acc); cudaFree(d.c0); cudaFree(d.qbuf); cudaFree(d.qcls); cudaFree(d.qcount);
   cudaFree(d.counters); cudaFree(d.rank_buf); cudaFree(d.staging); cudaFree(d.frame);
+  cudaFree(d.p3_text); cudaFree(d.p3_state);
+  for (int k = 0; k < 2; k++) { if (d.p3_pinned[k]) cudaFreeHost(d.p3_pinned[k]); if (d.p3_ev[k]) cudaEventDestroy(d.p3_ev[k]); }
   if (d.ev0) cudaEventDestroy(d.ev0);
   if (d.ev1) cudaEventDestroy(d.ev1);
   if (d.ev2) cudaEventDestroy(d.ev2);
@@ -590,6 +599,7 @@ int rt_render_device(int W, int H, void **dev_rgb_out, rt_stats *stats) {
     plans[0].launches += 1;
   }
   if (dev_rgb_out) *dev_rgb_out = d0.frame;
+  d0.frame_w = W; d0.frame_h = H;
   return collect_stats(n, W, H, plans, stats, ms_gather, t0);
 }
 
@@ -669,6 +679,153 @@ int rt_init_device(int ordinal) {
   CK(cudaMalloc((void **)&d.qcount, 8 * RT_CTL_STRIDE * sizeof(int)));
   CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
   g_ndev = 1;
+  return RT_OK;
+}
+
+}  // extern "C"
+
+// ==================================================================================
+// P3 writer (rt_p3.cuh): ppm_WriteOutP3 of C/ppm.c:168-184 with the formatting on the GPU.
+// ==================================================================================
+namespace {
+
+int p3_header(char *hdr, size_t cap, int W, int H, unsigned max_color) {
+  // fprintf(outFile, "P3\n"); fprintf(outFile, "%d %d \n%u\n", width, height, maxColor);  (C/ppm.c:171-172)
+  return snprintf(hdr, cap, "P3\n%d %d \n%u\n", W, H, max_color & 0xffu);   // maxColor is a uint8_t there
+}
+
+int p3_check(int W, int H) {
+  if (!g_ndev) return set_err(RT_ERR_NO_DEVICE, "P3 writer before rt_init (no GPU initialised; there is no CPU path)");
+  if (W <= 0 || H <= 0 || W > (1 << 26) || H > (1 << 26)) return set_err(RT_ERR_ARG, "bad image size %dx%d", W, H);
+  return RT_OK;
+}
+
+// Enqueue header copy + count + scan + emit on d.stream; d.p3_state = [n_spans + 1 offsets (u64)][n_spans lengths (u32)],
+// the end offset of the whole text lands in d.p3_state[*n_spans_out].
+int p3_enqueue(DeviceCtx &d, const uint8_t *dev_rgb, int W, int H, unsigned max_color, char *dev_text, size_t *n_spans_out) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(k_p3_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, P3_SMEM_BYTES));
+    attr_set = true;
+  }
+  char hdr[64];
+  const int hl = p3_header(hdr, sizeof hdr, W, H, max_color);
+  const unsigned long long n_values = (unsigned long long)W * (unsigned long long)H * 3ull;
+  const unsigned long long n_chunks = (n_values + P3_CHUNK - 1) / P3_CHUNK;
+  const unsigned long long n_spans = (n_chunks + P3_SPAN_CHUNKS - 1) / P3_SPAN_CHUNKS;
+  if (n_spans >= (1ull << 30)) return set_err(RT_ERR_ARG, "image too large for the P3 writer");
+  const size_t need = (size_t)(n_spans + 1) * sizeof(unsigned long long) + (size_t)n_spans * sizeof(unsigned) + 64;
+  size_t cap_bytes = d.p3_state_cap;
+  int r = dev_realloc(d.p3_state, cap_bytes, need);
+  d.p3_state_cap = cap_bytes;
+  if (r != RT_OK) return r;
+  unsigned long long *span_off = d.p3_state;
+  unsigned *span_len = (unsigned *)(d.p3_state + n_spans + 1);
+  CK(cudaMemsetAsync(span_len, 0, (size_t)n_spans * sizeof(unsigned), d.stream));
+  CK(cudaMemcpyAsync(dev_text, hdr, (size_t)hl, cudaMemcpyHostToDevice, d.stream));   // pageable source: staged before return
+  const unsigned long long gmax = 16ull * d.sm_count;
+  k_p3_count<<<(unsigned)(n_chunks < gmax ? n_chunks : gmax), P3_THREADS, 0, d.stream>>>(dev_rgb, n_values, n_chunks, span_len);
+  k_p3_scan<<<1, 1024, 0, d.stream>>>(span_len, span_off, (unsigned)n_spans, (unsigned long long)hl);
+  k_p3_emit<<<(unsigned)n_spans, P3_THREADS, P3_SMEM_BYTES, d.stream>>>(dev_rgb, n_values, n_chunks, span_off, (unsigned)n_spans, dev_text);
+  CK(cudaGetLastError());
+  if (n_spans_out) *n_spans_out = (size_t)n_spans;
+  return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t rt_p3_max_bytes(int W, int H) {
+  if (W <= 0 || H <= 0) return 0;
+  return (size_t)64 + (size_t)W * (size_t)H * 12u;   // header + 3 values x 4 bytes per pixel
+}
+
+int rt_p3_format_device(const void *dev_rgb, int W, int H, unsigned max_color, void *dev_text, size_t text_cap,
+                        size_t *text_bytes, rt_p3_stats *stats) {
+  int r = p3_check(W, H);
+  if (r != RT_OK) return r;
+  if (!dev_rgb || !dev_text || ((uintptr_t)dev_rgb & 15) || ((uintptr_t)dev_text & 15))
+    return set_err(RT_ERR_ARG, "rt_p3_format_device: NULL or not 16-byte aligned device pointer");
+  if (text_cap < rt_p3_max_bytes(W, H)) return set_err(RT_ERR_ARG, "rt_p3_format_device: text_cap below rt_p3_max_bytes");
+  const double t0 = now_ms();
+  DeviceCtx &d = g_dev[0];
+  CK(cudaSetDevice(d.dev));
+  CK(cudaEventRecord(d.ev0, d.stream));
+  // time the kernel alone: the resets go first
+  size_t n_spans = 0;
+  if ((r = p3_enqueue(d, (const uint8_t *)dev_rgb, W, H, max_color, (char *)dev_text, &n_spans)) != RT_OK) return r;
+  CK(cudaEventRecord(d.ev1, d.stream));
+  CK(cudaStreamSynchronize(d.stream));
+  unsigned long long total = 0;
+  CK(cudaMemcpy(&total, d.p3_state + n_spans, sizeof total, cudaMemcpyDeviceToHost));
+  if (text_bytes) *text_bytes = (size_t)total;
+  if (stats) {
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, d.ev0, d.ev1));
+    memset(stats, 0, sizeof *stats);
+    stats->text_bytes = total; stats->ms_format = ms; stats->ms_total = now_ms() - t0;
+  }
+  return RT_OK;
+}
+
+int rt_p3_write(const uint8_t *host_rgb, int W, int H, unsigned max_color, rt_p3_sink sink, void *user, rt_p3_stats *stats) {
+  int r = p3_check(W, H);
+  if (r != RT_OK) return r;
+  if (!sink) return set_err(RT_ERR_ARG, "rt_p3_write: sink is NULL");
+  const double t0 = now_ms();
+  DeviceCtx &d = g_dev[0];
+  CK(cudaSetDevice(d.dev));
+  const size_t n_values = (size_t)W * (size_t)H * 3u;
+  double ms_h2d = 0;
+  if (host_rgb) {
+    if ((r = dev_realloc(d.frame, d.frame_cap, n_values + 64)) != RT_OK) return r;
+    const double t1 = now_ms();
+    CK(cudaMemcpyAsync(d.frame, host_rgb, n_values, cudaMemcpyHostToDevice, d.stream));
+    CK(cudaStreamSynchronize(d.stream));
+    ms_h2d = now_ms() - t1;
+    d.frame_w = W; d.frame_h = H;
+  } else if (!d.frame || d.frame_w != W || d.frame_h != H) {
+    return set_err(RT_ERR_ARG, "rt_p3_write: no resident %dx%d frame (last render was %dx%d)", W, H, d.frame_w, d.frame_h);
+  }
+  if ((r = dev_realloc(d.p3_text, d.p3_text_cap, rt_p3_max_bytes(W, H) + 64)) != RT_OK) return r;
+  const size_t slab = (size_t)32 << 20;
+  if (d.p3_pinned_cap < slab) {
+    for (int k = 0; k < 2; k++) {
+      CK(cudaHostAlloc((void **)&d.p3_pinned[k], slab, cudaHostAllocDefault));
+      CK(cudaEventCreateWithFlags(&d.p3_ev[k], cudaEventDisableTiming));
+    }
+    d.p3_pinned_cap = slab;
+  }
+  CK(cudaEventRecord(d.ev0, d.stream));
+  size_t n_spans = 0;
+  if ((r = p3_enqueue(d, d.frame, W, H, max_color, d.p3_text, &n_spans)) != RT_OK) return r;
+  CK(cudaEventRecord(d.ev1, d.stream));
+  CK(cudaStreamSynchronize(d.stream));
+  unsigned long long total = 0;
+  CK(cudaMemcpy(&total, d.p3_state + n_spans, sizeof total, cudaMemcpyDeviceToHost));
+  // text -> host through two pinned slabs: the copy of slab k+1 overlaps the sink of slab k
+  const size_t n_slabs = ((size_t)total + slab - 1) / slab;
+  int sink_rc = 0;
+  for (size_t k = 0; k <= n_slabs && !sink_rc; k++) {
+    if (k < n_slabs) {
+      const size_t off = k * slab, nb = (size_t)total - off < slab ? (size_t)total - off : slab;
+      CK(cudaMemcpyAsync(d.p3_pinned[k & 1], d.p3_text + off, nb, cudaMemcpyDeviceToHost, d.stream));
+      CK(cudaEventRecord(d.p3_ev[k & 1], d.stream));
+    }
+    if (k > 0) {
+      const size_t off = (k - 1) * slab, nb = (size_t)total - off < slab ? (size_t)total - off : slab;
+      CK(cudaEventSynchronize(d.p3_ev[(k - 1) & 1]));
+      sink_rc = sink(d.p3_pinned[(k - 1) & 1], nb, user);
+    }
+  }
+  CK(cudaStreamSynchronize(d.stream));
+  if (sink_rc) return set_err(RT_ERR_ARG, "rt_p3_write: the sink reported failure (%d)", sink_rc);
+  if (stats) {
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, d.ev0, d.ev1));
+    stats->text_bytes = total; stats->ms_h2d = ms_h2d; stats->ms_format = ms; stats->ms_total = now_ms() - t0;
+  }
   return RT_OK;
 }
 

@@ -1,35 +1,46 @@
 /*
- * host/ppm_out.c -- byte-exact P3 writer (format of C/ppm.c:168-184):
- *     "P3\n" "<w> <h> \n" "<maxColor>\n"   then one decimal per line, R G B per pixel.
- * (the space before the second newline is the reference's.)  The reference calls
- * fprintf once per pixel (~0.2 s per Mpixel); this one formats through a 256-entry
- * table into a 4 MiB buffer, and indexes with size_t so 32768^2 images work.
+ * host/ppm_out.c -- ppm_WriteOutP3 of the reference (C/ppm.c:168-184), same signature, same
+ * bytes:  "P3\n" "<w> <h> \n" "<maxColor>\n"  then one decimal per line, R G B per pixel
+ * (the space before the second newline is the reference's).  The reference calls fprintf
+ * once per pixel (~0.2 s per Mpixel: 54 s for a 16384^2 frame); here the text is produced by
+ * the GPU formatter behind rt_p3_write (csrc/rt_p3.cuh) and this file only fwrite()s the
+ * pieces.  No CPU formatter exists: without a GPU the call fails loudly like raycast().
+ *
+ * Which pixels: the pixmap the caller passes, uploaded first -- correct for any caller.  A
+ * caller that has not touched the pixmap since raycast() filled it (the reference's main,
+ * C/raycast.c:57-59, and this repo's CLI) may say so with rt_host_p3_resident(1): the frame
+ * raycast() left on GPU 0 is formatted directly and the upload is skipped.
  */
 #include <stdlib.h>
 #include <string.h>
 #include "ppm_out.h"
+#include "rt_abi.h"
+
+static int g_resident = 0;
+static rt_p3_stats g_p3_stats;
+
+void rt_host_p3_resident(int yes) { g_resident = yes; }
+const rt_p3_stats *rt_host_last_p3_stats(void) { return &g_p3_stats; }
+
+static int file_sink(const void *data, size_t nbytes, void *user) {
+  return fwrite(data, 1, nbytes, (FILE *)user) == nbytes ? 0 : 1;
+}
 
 void ppm_WriteOutP3(PPMFormat inData, FILE *outFile) {
-  char lut[256][8];   /* "255\n" + NUL needs 5 */
-  uint8_t lut_len[256];
-  for (int v = 0; v < 256; v++) lut_len[v] = (uint8_t)sprintf(lut[v], "%d\n", v);
-
-  fprintf(outFile, "P3\n%d %d \n%u\n", inData.width, inData.height, inData.maxColor);
-
-  const size_t total = (size_t)inData.width * (size_t)inData.height * 3u;
-  const size_t cap = (size_t)4 << 20;
-  char *buf = (char *)malloc(cap + 8);
-  if (!buf) { fprintf(stderr, "Error: out of memory in ppm_WriteOutP3\n"); exit(1); }
-  size_t fill = 0;
-  const uint8_t *src = inData.pixmap;
-  for (size_t i = 0; i < total; i++) {
-    const uint8_t v = src[i];
-    memcpy(buf + fill, lut[v], 4);
-    fill += lut_len[v];
-    if (fill >= cap) { fwrite(buf, 1, fill, outFile); fill = 0; }
+  if (rt_device_count() == 0) {
+    const char *g = getenv("RT_GPUS");
+    if (rt_init(g ? atoi(g) : 1) != RT_OK) {
+      fprintf(stderr, "Error: cannot initialise the B200 library for the P3 writer: %s\n", rt_last_error());
+      exit(1);
+    }
   }
-  if (fill) fwrite(buf, 1, fill, outFile);
-  free(buf);
+  int r = RT_ERR_ARG;
+  if (g_resident) r = rt_p3_write(NULL, inData.width, inData.height, inData.maxColor, file_sink, outFile, &g_p3_stats);
+  if (r != RT_OK) r = rt_p3_write(inData.pixmap, inData.width, inData.height, inData.maxColor, file_sink, outFile, &g_p3_stats);
+  if (r != RT_OK) {
+    fprintf(stderr, "Error: P3 write failed: %s\n", rt_last_error());
+    exit(1);
+  }
 }
 
 void ppm_WriteOutP6(PPMFormat inData, FILE *outFile) {

@@ -67,6 +67,7 @@ int main(int argc, char **argv) {
   double start = now_sec();
   raycast(json_struct, photo_data);
   double rendered = now_sec();
+  rt_host_p3_resident(1);   /* nothing touched the pixmap since raycast() (as in C/raycast.c:57-59) */
   if (getenv("RT_PPM_P6")) ppm_WriteOutP6(photo_data, output_image);
   else ppm_WriteOutP3(photo_data, output_image);
   fclose(output_image);

@@ -123,3 +123,49 @@ def compare(a, b):
 
 def fvec(*v):
     return (C.c_float * len(v))(*v)
+
+
+def oracle_p3(pixmap, W, H, max_color=255):
+    """P3 text of a pixmap by the CPU restatement (oracle/rt_oracle.c: orc_p3_format)."""
+    o = oracle()
+    o.orc_p3_format.restype = C.c_size_t
+    o.orc_p3_format.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_size_t]
+    pixmap = np.ascontiguousarray(pixmap, dtype=np.uint8)
+    assert pixmap.size == W * H * 3
+    cap = 64 + 4 * pixmap.size + 16
+    buf = C.create_string_buffer(cap)
+    n = o.orc_p3_format(pixmap.ctypes.data_as(C.c_void_p), W, H, max_color, buf, cap)
+    assert n > 0
+    return buf.raw[:n]
+
+
+def ref_p3(pixmap, W, H, max_color=255):
+    """P3 file written by the reference's own ppm_WriteOutP3 (oracle/_ref/libref.so)."""
+    import tempfile
+    r = ref()
+    r.ref_write_p3.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    pixmap = np.ascontiguousarray(pixmap, dtype=np.uint8)
+    with tempfile.NamedTemporaryFile(suffix=".ppm") as f:
+        assert r.ref_write_p3(os.fsencode(f.name), W, H, max_color, pixmap.ctypes.data_as(C.c_void_p)) == 0
+        return open(f.name, "rb").read()
+
+
+def p3_pixmap(W, H, kind, seed=7):
+    """Seeded test pixmaps for the P3 writer: every text length and chunk-boundary pattern."""
+    n = W * H * 3
+    rng = np.random.default_rng(seed)
+    if kind == "random":
+        a = rng.integers(0, 256, n, dtype=np.uint8)
+    elif kind == "zeros":
+        a = np.zeros(n, dtype=np.uint8)
+    elif kind == "max":
+        a = np.full(n, 255, dtype=np.uint8)
+    elif kind == "ramp":
+        a = (np.arange(n) % 256).astype(np.uint8)
+    elif kind == "edges":      # the length boundaries 0/9/10/99/100/255 in random order
+        a = rng.choice(np.array([0, 9, 10, 99, 100, 255], dtype=np.uint8), n)
+    elif kind == "runs":       # long runs of one length class, so whole chunks are 2, 3 or 4 bytes per value
+        a = np.repeat(rng.choice(np.array([5, 50, 200], dtype=np.uint8), n // 3000 + 1), 3000)[:n]
+    else:
+        raise ValueError(kind)
+    return a.reshape(H, W, 3)

@@ -1,4 +1,4 @@
-"""CPU tests of the host side: parser parity and error paths, P3 writer bytes, the C-ABI
+"""CPU tests of the host side: parser parity and error paths, the C-ABI
 library's exported symbols, band ownership helpers, loud failure without a GPU."""
 import ctypes as C
 import os
@@ -146,23 +146,3 @@ def test_cli_usage_and_open_errors(tmp_path):
     assert r.returncode == 1 and r.stderr.startswith("Error: Unable to open the input scene file: ")
     r = subprocess.run([exe, "4", "4", scene_path("simple"), str(tmp_path / "nodir" / "o.ppm")], capture_output=True, text=True)
     assert r.returncode == 1 and r.stderr.startswith("Error: Unable to open the output image file: ")
-
-
-def test_p3_writer_bytes(tmp_path):
-    h = pkg.load_host_library()
-
-    class PPM(C.Structure):
-        _fields_ = [("width", C.c_int), ("height", C.c_int), ("size", C.c_int), ("maxColor", C.c_uint8),
-                    ("depth", C.c_uint8), ("tupleType", C.c_char_p), ("pixmap", C.POINTER(C.c_uint8))]
-    libc = C.CDLL(None)
-    libc.fopen.restype = C.c_void_p
-    libc.fopen.argtypes = [C.c_char_p, C.c_char_p]
-    libc.fclose.argtypes = [C.c_void_p]
-    h.ppm_WriteOutP3.argtypes = [PPM, C.c_void_p]
-    px = np.arange(7 * 5 * 3, dtype=np.uint8) * 37
-    out = tmp_path / "w.ppm"
-    f = libc.fopen(os.fsencode(out), b"wb")
-    h.ppm_WriteOutP3(PPM(7, 5, 105, 255, 3, None, px.ctypes.data_as(C.POINTER(C.c_uint8))), f)
-    libc.fclose(f)
-    expect = b"P3\n7 5 \n255\n" + b"".join(b"%d\n" % v for v in px.tolist())
-    assert out.read_bytes() == expect
