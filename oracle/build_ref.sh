@@ -32,3 +32,14 @@ gcc $CFLAGS "$TMP/raycast_p1.c" $SUPPORT -o "$OUT/raytrace_asis" -lm
 gcc $CFLAGS -fPIC -shared -DREF_RAYCAST_C="\"$TMP/raycast_patched.c\"" \
     "$HERE/ref_harness.c" $SUPPORT -o "$OUT/libref.so" -lm -lpthread
 echo "built: $(ls "$OUT")"
+# Context comparator: the reference's own CUDA variant, unmodified, rebuilt for
+# sm_100a (its Makefile targets sm_75).  Timed by tools/gpu_refcuda.sh on C1-C3 only: its shared-memory
+# scene loader and MAX_SHAPES 128 (CUDA/raycast.cu:14,123) rule out C4/C5.
+CU="${RT_REF:-/root/reference}/CUDA"
+if [ -f "$CU/raycast.cu" ] && command -v nvcc >/dev/null 2>&1; then
+  (cd "$CU" && nvcc -O3 -rdc=true -w -gencode=arch=compute_100a,code=sm_100a raycast.cu v3math.cu ppm.cu parse.cu objects.cu \
+      -o "$OUT/raytrace_refcuda" --objdir-as-tempdir 2>/dev/null) || \
+  (cd "$TMP" && nvcc -O3 -rdc=true -w -gencode=arch=compute_100a,code=sm_100a "$CU/raycast.cu" "$CU/v3math.cu" "$CU/ppm.cu" "$CU/parse.cu" "$CU/objects.cu" \
+      -I"$CU" -o "$OUT/raytrace_refcuda") || echo "build_ref.sh: reference CUDA variant did not build (context only)" >&2
+fi
+echo "built: $(ls "$OUT" | tr '\n' ' ')"

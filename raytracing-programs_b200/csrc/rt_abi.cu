@@ -157,6 +157,16 @@ void free_device(DeviceCtx &d) {
   d = DeviceCtx();
 }
 
+// CUDA loads kernels lazily: touch every kernel once at init so the first render does not pay for it.
+void warm_modules() {
+  cudaFuncAttributes fa;
+  cudaFuncGetAttributes(&fa, k_primary); cudaFuncGetAttributes(&fa, k_finalize); cudaFuncGetAttributes(&fa, k_assemble);
+  cudaFuncGetAttributes(&fa, k_shade<1>); cudaFuncGetAttributes(&fa, k_shade<2>); cudaFuncGetAttributes(&fa, k_shade<4>);
+  cudaFuncGetAttributes(&fa, k_shade<8>); cudaFuncGetAttributes(&fa, k_shade<16>);
+  cudaFuncGetAttributes(&fa, k_p3_count); cudaFuncGetAttributes(&fa, k_p3_scan); cudaFuncGetAttributes(&fa, k_p3_emit);
+  cudaGetLastError();
+}
+
 }  // namespace
 
 // ==================================================================================
@@ -218,6 +228,7 @@ int rt_init(int n_gpus) {
     CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
     CK(cudaMalloc((void **)&d.qcount, 8 * RT_CTL_STRIDE * sizeof(int)));
     CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
+    warm_modules();
   }
   g_ndev = n;
   if (n > 1) {
@@ -678,6 +689,7 @@ int rt_init_device(int ordinal) {
   CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
   CK(cudaMalloc((void **)&d.qcount, 8 * RT_CTL_STRIDE * sizeof(int)));
   CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
+  warm_modules();
   g_ndev = 1;
   return RT_OK;
 }
