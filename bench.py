@@ -196,6 +196,35 @@ def p3_leg(r, W, H, frame, flush, pk, host_frame, cpu=True):
     return leg
 
 
+def ingest_leg(r, cpu=True):
+    """Scene ingest on the 4096-object C5 scene: parse (host C parser, same grammar as
+    C/parse.c) + flatten + SoA build + H2D upload; next to the reference parser's time for the same file."""
+    path = WORKLOADS["c5"][1]
+    t_parse, t_upload = [], []
+    for _ in range(5):
+        t0 = time.perf_counter()
+        sc = pkg.load_scene(path)
+        t1 = time.perf_counter()
+        r.upload(sc)
+        t2 = time.perf_counter()
+        t_parse.append((t1 - t0) * 1e3)
+        t_upload.append((t2 - t1) * 1e3)
+    leg = {"scene": os.path.basename(path), "shapes": sc.num_shapes, "lights": sc.num_lights, "file_bytes": os.path.getsize(path),
+           "parse_flatten_ms": statistics.median(t_parse), "soa_upload_ms": statistics.median(t_upload)}
+    if cpu:
+        import rtlib
+        if rtlib.ref_available():
+            ref = rtlib.ref()
+            ts = []
+            for _ in range(5):
+                t0 = time.perf_counter()
+                h = ref.ref_scene_load(os.fsencode(path))
+                ts.append((time.perf_counter() - t0) * 1e3)
+                ref.ref_scene_free(h)
+            leg["reference_parse_ms"] = statistics.median(ts)
+    return leg
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -389,6 +418,9 @@ def main():
     # ---- P3 writer: HBM-bound formatter on the same frame -------
     if world == 1 and not args.no_extra:
         out["p3_writer"] = p3_leg(r, W, H, frame, flush, pk, host_frame, cpu=not args.no_cpu)
+    if world == 1 and not args.no_extra:
+        out["scene_ingest"] = ingest_leg(r, cpu=not args.no_cpu)
+        r.upload(sc)
     # ---- the small shipped configs, for the record (N = 1 only) --------------------------
     if world == 1 and not args.no_extra and not args.size:
         extra = {}

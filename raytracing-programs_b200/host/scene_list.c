@@ -3,7 +3,9 @@
  * (C/objects.h:63-73; behaviour of C/objects.c:20-221): tail append in file order,
  * plane/quadric refractivity 0 and ior 1, cos_theta = cos(theta) in double.
  * New implementation: iterative (the reference recurses once per node, which is a
- * stack hazard on the 4096-object synthetic scenes) and zero-initialised nodes.
+ * stack hazard on the 4096-object synthetic scenes), zero-initialised nodes, and the tail of
+ * the list being built is remembered, so appending n objects is O(n) instead of the
+ * reference's O(n^2) walk (C/objects.c:40).
  */
 #include <math.h>
 #include <string.h>
@@ -24,11 +26,16 @@ static shape_t *shape_node(shape_type_t type, const float *diffuse, const float 
   return n;
 }
 
+/* Tail cache: valid while the same head keeps being appended to; dropped by free_*_list. */
+static shape_t *g_shape_head, *g_shape_tail;
+static light_t *g_light_head, *g_light_tail;
+
 static shape_t *shape_append(shape_t *head, shape_t *n) {
-  if (!head) return n;
-  shape_t *t = head;
+  if (!head) { g_shape_head = g_shape_tail = n; return n; }
+  shape_t *t = (head == g_shape_head && g_shape_tail && !g_shape_tail->next) ? g_shape_tail : head;
   while (t->next) t = t->next;
   t->next = n;
+  g_shape_head = head; g_shape_tail = n;
   return head;
 }
 
@@ -60,10 +67,11 @@ shape_t *add_new_quadric(shape_t *head, float *diffuse, float *specular, float a
 }
 
 static light_t *light_append(light_t *head, light_t *n) {
-  if (!head) return n;
-  light_t *t = head;
+  if (!head) { g_light_head = g_light_tail = n; return n; }
+  light_t *t = (head == g_light_head && g_light_tail && !g_light_tail->next) ? g_light_tail : head;
   while (t->next) t = t->next;
   t->next = n;
+  g_light_head = head; g_light_tail = n;
   return head;
 }
 
@@ -93,11 +101,13 @@ light_t *add_new_spot_light(light_t *head, float *color, float *position, float 
 }
 
 shape_t *free_shape_list(shape_t *head) {
+  g_shape_head = g_shape_tail = NULL;
   while (head) { shape_t *nx = head->next; free(head); head = nx; }
   return NULL;
 }
 
 light_t *free_light_list(light_t *head) {
+  g_light_head = g_light_tail = NULL;
   while (head) { light_t *nx = head->next; free(head); head = nx; }
   return NULL;
 }

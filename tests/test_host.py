@@ -4,6 +4,7 @@ import ctypes as C
 import os
 import re
 import subprocess
+import time
 
 import numpy as np
 import pytest
@@ -146,3 +147,33 @@ def test_cli_usage_and_open_errors(tmp_path):
     assert r.returncode == 1 and r.stderr.startswith("Error: Unable to open the input scene file: ")
     r = subprocess.run([exe, "4", "4", scene_path("simple"), str(tmp_path / "nodir" / "o.ppm")], capture_output=True, text=True)
     assert r.returncode == 1 and r.stderr.startswith("Error: Unable to open the output image file: ")
+
+
+def test_parser_hardening(tmp_path):
+    """inputs that crash or hang the reference parser (8c 'known fragilities') are read
+    here without changing what well-formed files mean: fields longer than the reference's 100-byte buffers, a
+    field without ':', an unclosed '[', no trailing newline, CRLF-free blank lines, and a 5000-object file
+    (the reference appends recursively, one stack frame per node)."""
+    long_val = "0." + "0" * 150 + "5"                        # > 99 characters in one field
+    p = tmp_path / "h.scene"
+    p.write_text("camera, width: 2, height: 2\n"
+                 f"sphere, radius: 1, position: [0, 0, -5], diffuse_color: [{long_val}, 1, 0], reflectivity: 0, refractivity: 0, ior: 1\n"
+                 "sphere, radius: 1, stray field, position: [1, 0, -5], reflectivity: 0, refractivity: 0, ior: 1\n"
+                 "plane, normal: [0, 1, 0], position: [0, -1, 0, reflectivity: 0\n"
+                 "light, color: [1, 1, 1], position: [0, 3, 0], radial-a0: 1, radial-a1: 0, radial-a2: 0")
+    r = subprocess.run([os.path.join(BIN, "scene_dump"), str(p)], capture_output=True, text=True, timeout=20)
+    # the unclosed '[' swallows the rest of its line: the plane then lacks reflectivity -> the reference's message
+    assert r.returncode == 1 and r.stderr.strip() == "Error: A field for a plane was missing."
+    p.write_text(p.read_text().replace("position: [0, -1, 0, reflectivity", "position: [0, -1, 0], reflectivity"))
+    sc = pkg.load_scene(str(p))
+    assert sc.num_shapes == 3 and sc.num_lights == 1
+    assert abs(sc.shapes[0].diffuse[0] - float(long_val)) < 1e-12 and sc.shapes[1].position[0] == 1.0
+    big = tmp_path / "big.scene"
+    lines = ["camera, width: 2, height: 2"] + [
+        f"sphere, radius: 0.5, position: [{i % 70 - 35}, {i // 70 - 35}, -50], diffuse_color: [1, 0, 0], reflectivity: 0, refractivity: 0, ior: 1"
+        for i in range(5000)]
+    big.write_text("\n".join(lines))
+    t0 = time.perf_counter()
+    sc = pkg.load_scene(str(big))
+    assert sc.num_shapes == 5000 and sc.shapes[4999].position[0] == float(4999 % 70 - 35)
+    assert time.perf_counter() - t0 < 5.0
