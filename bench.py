@@ -340,8 +340,9 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    rays_p, rays_r, rays_s, hitp, flops, launches = allsum([agg.rays_primary, agg.rays_reflection, agg.rays_shadow,
-                                                             agg.hit_points, agg.flops, agg.kernel_launches])
+    rays_p, rays_r, rays_s, hitp, flops, launches, t_so, t_sd, t_qo, t_qd, t_slots = allsum(
+        [agg.rays_primary, agg.rays_reflection, agg.rays_shadow, agg.hit_points, agg.flops, agg.kernel_launches,
+         agg.sphere_tests_o, agg.sphere_tests_d, agg.quadric_tests_o, agg.quadric_tests_d, agg.scan_slots])
     rays = rays_p + rays_r + rays_s
     ms_step = allmax(dev_ms / args.steps)
     wall_step = allmax(wall_ms / args.steps)
@@ -387,7 +388,9 @@ def main():
            "config": {"workload": name, "width": W, "height": H, "shapes": sc.num_shapes, "lights": sc.num_lights,
                       "parallelism": f"row bands of {pkg.load_library().rt_band_height()} rows interleaved over {world} GPU(s)",
                       "l2": "256 MB flush between timed steps; per-tile working set > L2",
-                      "rays_per_pixel": rays / (W * H), "rays": {"primary": rays_p, "reflection": rays_r, "shadow": rays_s}},
+                      "rays_per_pixel": rays / (W * H), "rays": {"primary": rays_p, "reflection": rays_r, "shadow": rays_s},
+                      "scan": {"hit_points": hitp, "live_rays_per_primitive_scanned": (t_sd + t_qd) / max(t_so + t_qo, 1),
+                               "slots_per_primitive_scanned": t_slots / max(t_so + t_qo, 1)}},
            "mpixels_per_s": W * H / ms_step / 1e3, "tflops_fp32_algorithmic": flops / ms_step / 1e9,
            "frac_fp32_peak": flops / ms_step / 1e9 / (pk["fp32_tflops"] * world),
            "roofline": roof, "e2e": e2e, "gpu_launches": int(launches * args.steps + (args.steps if world > 1 else 0)),

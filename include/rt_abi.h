@@ -102,6 +102,8 @@ typedef struct rt_stats {
   uint64_t launches_shade;
   double ms_gather;             /* band gather to GPU 0 */
   double ms_total;              /* the whole call, host clock */
+  uint64_t scan_slots;          /* ray slots x primitives the bundle scans executed (>= the *_tests_d sum:
+                                   slots of rays already occluded, or padding, still ride along) */
 } rt_stats;
 
 /* Initialise n_gpus devices (0 = all visible). Safe to call again after rt_shutdown. */

@@ -42,7 +42,8 @@ class RtStats(C.Structure):
         "quadric_tests_o", "quadric_tests_d", "kernel_launches")] + [
         ("flops", C.c_double), ("flops_shade", C.c_double), ("ms_kernels", C.c_double),
         ("ms_primary", C.c_double), ("ms_shade", C.c_double), ("ms_finalize", C.c_double),
-        ("launches_shade", C.c_uint64), ("ms_gather", C.c_double), ("ms_total", C.c_double)]
+        ("launches_shade", C.c_uint64), ("ms_gather", C.c_double), ("ms_total", C.c_double),
+        ("scan_slots", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -12,6 +12,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <sys/time.h>
+#include <algorithm>
 #include <vector>
 
 #include "rt_abi.h"
@@ -161,8 +162,10 @@ void free_device(DeviceCtx &d) {
 void warm_modules() {
   cudaFuncAttributes fa;
   cudaFuncGetAttributes(&fa, k_primary); cudaFuncGetAttributes(&fa, k_finalize); cudaFuncGetAttributes(&fa, k_assemble);
-  cudaFuncGetAttributes(&fa, k_shade<1>); cudaFuncGetAttributes(&fa, k_shade<2>); cudaFuncGetAttributes(&fa, k_shade<4>);
-  cudaFuncGetAttributes(&fa, k_shade<8>); cudaFuncGetAttributes(&fa, k_shade<16>);
+  cudaFuncGetAttributes(&fa, k_shade<1, true>); cudaFuncGetAttributes(&fa, k_shade<2, true>); cudaFuncGetAttributes(&fa, k_shade<4, true>);
+  cudaFuncGetAttributes(&fa, k_shade<8, true>); cudaFuncGetAttributes(&fa, k_shade<16, true>);
+  cudaFuncGetAttributes(&fa, k_shade<1, false>); cudaFuncGetAttributes(&fa, k_shade<2, false>); cudaFuncGetAttributes(&fa, k_shade<4, false>);
+  cudaFuncGetAttributes(&fa, k_shade<8, false>); cudaFuncGetAttributes(&fa, k_shade<16, false>);
   cudaFuncGetAttributes(&fa, k_p3_count); cudaFuncGetAttributes(&fa, k_p3_scan); cudaFuncGetAttributes(&fa, k_p3_emit);
   cudaGetLastError();
 }
@@ -252,6 +255,7 @@ int rt_scene_upload(const rt_scene *scene) {
   std::vector<float4> sph, sph_hot, sph_prim, pln, quad, quad_hot, quad_prim, mat(2 * (size_t)n + 1), lights(4 * (size_t)nl + 1);
   std::vector<int> sph_idx, pln_idx, quad_idx;
   std::vector<int2> slot((size_t)n + 1);
+  std::vector<int> sphere_order;
   for (int i = 0; i < n; i++) {
     const rt_shape &s = scene->shapes[i];
     // opacity, C/raycast.c:383: 1.0 - reflectivity - refractivity in double, stored float
@@ -259,23 +263,7 @@ int rt_scene_upload(const rt_scene *scene) {
     mat[2 * i] = make_float4(s.diffuse[0], s.diffuse[1], s.diffuse[2], s.reflectivity);
     mat[2 * i + 1] = make_float4(s.specular[0], s.specular[1], s.specular[2], opacity);
     if (s.type == RT_SPHERE) {
-      slot[i] = make_int2(0, (int)sph.size());
-      const float r = s.params[0];
-      sph.push_back(make_float4(s.position[0], s.position[1], s.position[2], r));
-      { volatile float rr = r * r; sph_hot.push_back(make_float4(s.position[0], s.position[1], s.position[2], rr)); }
-      // primary rays start at exactly (0,0,0): temp = o - centre and c of C/raycast.c:581,585
-      volatile float t0 = 0.0f - s.position[0], t1 = 0.0f - s.position[1], t2 = 0.0f - s.position[2];
-      volatile float p0 = t0 * t0, p1 = t1 * t1, p2 = t2 * t2;
-      volatile float s01 = p0 + p1;
-      volatile float tt = s01 + p2;
-      // reject-filter constant k = 2^-18 (T' + r^2) - (T' - r^2), same formula as k_shade's
-      (void)tt;
-      volatile float rr2 = r * r;
-      volatile float q0 = t0 * t0;
-      volatile float Tp = fmaf(t2, t2, fmaf(t1, t1, q0));
-      volatile float su = Tp + rr2, di = rr2 - Tp;
-      sph_prim.push_back(make_float4(t0, t1, t2, fmaf(RT_FILTER_EPS, su, di)));
-      sph_idx.push_back(i);
+      sphere_order.push_back(i);
     } else if (s.type == RT_PLANE) {
       slot[i] = make_int2(1, (int)pln_idx.size());
       pln.push_back(make_float4(s.position[0], s.position[1], s.position[2], 0.f));
@@ -302,6 +290,34 @@ int rt_scene_upload(const rt_scene *scene) {
     } else {
       return set_err(RT_ERR_ARG, "shape %d has unknown type %d", i, s.type);
     }
+  }
+  // Spheres in descending radius (stable): big occluders first, so shadow rays die early in the
+  // scan and k_shade can drop to a smaller scan variant.  Any order is parity-safe: nearest hit
+  // is the lexicographic (t, original index) minimum and a shadow query is any-hit.
+  std::stable_sort(sphere_order.begin(), sphere_order.end(), [&](int x, int y) {
+    const float rx = scene->shapes[x].params[0], ry = scene->shapes[y].params[0];
+    return (rx == rx ? rx : -INFINITY) > (ry == ry ? ry : -INFINITY);   // NaN radii last
+  });
+  if (getenv("RT_NO_SORT")) std::sort(sphere_order.begin(), sphere_order.end());
+  for (int i : sphere_order) {
+    const rt_shape &s = scene->shapes[i];
+    slot[i] = make_int2(0, (int)sph.size());
+    const float r = s.params[0];
+    sph.push_back(make_float4(s.position[0], s.position[1], s.position[2], r));
+    { volatile float rr = r * r; sph_hot.push_back(make_float4(s.position[0], s.position[1], s.position[2], rr)); }
+    // primary rays start at exactly (0,0,0): temp = o - centre and c of C/raycast.c:581,585
+    volatile float t0 = 0.0f - s.position[0], t1 = 0.0f - s.position[1], t2 = 0.0f - s.position[2];
+    volatile float p0 = t0 * t0, p1 = t1 * t1, p2 = t2 * t2;
+    volatile float s01 = p0 + p1;
+    volatile float tt = s01 + p2;
+    // reject-filter constant k = 2^-18 (T' + r^2) - (T' - r^2), same formula as k_shade's
+    (void)tt;
+    volatile float rr2 = r * r;
+    volatile float q0 = t0 * t0;
+    volatile float Tp = fmaf(t2, t2, fmaf(t1, t1, q0));
+    volatile float su = Tp + rr2, di = rr2 - Tp;
+    sph_prim.push_back(make_float4(t0, t1, t2, fmaf(RT_FILTER_EPS, su, di)));
+    sph_idx.push_back(i);
   }
   const size_t slot_count_spheres = sph_idx.size();
   for (int l = 0; l < nl; l++) {
@@ -382,14 +398,16 @@ namespace {
 template <int LB>
 int shade_grid(DeviceCtx &d) {
   int per_sm = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_shade<LB>, 128, 0);
+  if (d.sc.n_quadrics > 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_shade<LB, true>, 128, 0);
+  else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_shade<LB, false>, 128, 0);
   if (per_sm < 1) per_sm = 1;
   return per_sm * d.sm_count;
 }
 
 template <int LB>
 void launch_shade(DeviceCtx &d, int grid, int level, HitQueue qin, HitQueue qout) {
-  k_shade<LB><<<grid, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters);
+  if (d.sc.n_quadrics > 0) k_shade<LB, true><<<grid, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters);
+  else k_shade<LB, false><<<grid, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters);
 }
 
 int pick_lb(int n_lights) {
@@ -510,6 +528,7 @@ int collect_stats(int ndev, int W, int H, const RankPlan *plans, rt_stats *st, d
     s.plane_tests_o += c[CT_PLN_O]; s.plane_tests_d += c[CT_PLN_D];
     s.quadric_tests_o += c[CT_QUAD_O]; s.quadric_tests_d += c[CT_QUAD_D];
     s.kernel_launches += plans[i].launches;
+    s.scan_slots += c[CT_SLOTS];
     // SURVEY.md section 8a flop convention
     const double all = 10.0 * c[CT_SPH_O] + 8.0 * c[CT_SPH_D] + 8.0 * c[CT_PLN_O] + 6.0 * c[CT_PLN_D] +
                21.0 * c[CT_QUAD_O] + 37.0 * c[CT_QUAD_D] + 3.0 * c[CT_CANDIDATES] +

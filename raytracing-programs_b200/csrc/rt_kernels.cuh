@@ -13,6 +13,11 @@
 #ifndef RT_SHADE_MINB
 #define RT_SHADE_MINB 4
 #endif
+#ifndef RT_VSTEP
+#define RT_VSTEP 4       /* the bundle scans are compiled for NR, NR - RT_VSTEP, ... ray slots.  Measured on C4:
+                            step 2 executes 10 % fewer slots but k_shade<16> grows from 7.9 k to 13.5 k
+                            instructions and the frame gets 37 % slower (instruction cache) */
+#endif
 #define RT_CHUNK 128     /* spheres per scan chunk = capacity of the per-thread survivor queue */
 #define RT_INF __int_as_float(0x7f800000)
 #define RT_NAN __int_as_float(0x7fc00000)
@@ -281,6 +286,8 @@ RT_DEV void scan_chunk(const float (*dsm)[128], unsigned char (*cand)[128], cons
     const float T1 = __fmaf_rn(z1, z1, __fmaf_rn(y1, y1, x1 * x1));
     const float ka0 = __fmaf_rn(-RT_FILTER_EPS, T0 + g0.w, T0 - g0.w);
     const float ka1 = __fmaf_rn(-RT_FILTER_EPS, T1 + g1.w, T1 - g1.w);
+    // (a one-sided variant -- only max(-e) for spheres the origin is certainly outside of -- halves the
+    // survivors but costs four more instructions per sphere: measured 3 % slower on C4, not kept)
     float mx0 = 0.0f, mx1 = 0.0f;
     #pragma unroll
     for (int j = 0; j < NRV; j++) {
@@ -401,20 +408,43 @@ RT_DEV void scan_quadrics(const float (*dsm)[128], unsigned char (*cand)[128], c
   }
 }
 
-template <int LB>
+// Scan variants: the bundle scans are compiled for NR, NR-2, NR-4, ... >= 3 ray slots; a warp runs
+// the smallest one that holds the largest number of rays any of its hit points still has alive.
+template <int NRV, int NRMIN>
+RT_DEV void scan_spheres_v(const int nrv, const float (*dsm)[128], unsigned char (*cand)[128], const int tid, const v3 P,
+                           const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
+                           unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
+  if constexpr (NRV - RT_VSTEP >= NRMIN) {
+    if (nrv < NRV) { scan_spheres_v<NRV - RT_VSTEP, NRMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand); return; }
+  }
+  scan_chunk<NRV>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+}
+template <int NRV, int NRMIN>
+RT_DEV void scan_quadrics_v(const int nrv, const float (*dsm)[128], unsigned char (*cand)[128], const int tid, const v3 P,
+                            const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
+                            unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
+  if constexpr (NRV - RT_VSTEP >= NRMIN) {
+    if (nrv < NRV) { scan_quadrics_v<NRV - RT_VSTEP, NRMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand); return; }
+  }
+  scan_quadrics<NRV>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+}
+
+// QUADS = false: compiled without the quadric sections for scenes that have none (half the code:
+// the instruction cache is the scarce resource of this kernel).
+template <int LB, bool QUADS>
 __global__ void __launch_bounds__(128, RT_SHADE_MINB)
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
         float4 *__restrict__ c0, unsigned long long *__restrict__ counters) {
   constexpr int NR = LB + 1;
-  // ray-slot counts the scan is compiled for; a warp runs the smallest one that holds the
-  // largest number of live rays any of its hit points has
-  constexpr int V3 = NR, V2 = NR > 5 ? NR - 4 : NR, V1 = NR > 9 ? NR - 8 : V2, V0 = NR > 13 ? NR - 12 : V1;
+  constexpr int VMIN = NR >= 3 ? NR - RT_VSTEP * ((NR - 3) / RT_VSTEP) : NR;   // smallest compiled variant
+  auto pick_variant = [](int live) { const int v = NR - RT_VSTEP * ((NR - live) / RT_VSTEP); return v < VMIN ? VMIN : v; };
   __shared__ unsigned char cand[RT_CHUNK + 1][128];   // +1: the branch-free push stores before it knows
   __shared__ float dsm[3 * NR][128];
   const int tid = threadIdx.x;
   // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
   // counters are products of these with the scene's primitive counts, formed at the end
-  unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_live_sum = 0, n_ls = 0, n_cand = 0;
+  unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_ls = 0, n_cand = 0;
+  unsigned d_sph = 0, d_pln = 0, d_quad = 0, d_slots = 0;   // direction tests executed: live ray slots x primitives scanned with them
   // Dynamic scheduling: every warp claims 32 consecutive entries of one class list at a time
   // (heaviest class first), so no SM idles while another still holds a backlog, and the hit
   // points a warp shades together need about the same number of ray slots.
@@ -485,22 +515,38 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
         }
       }
       const int wmax = __reduce_max_sync(vmask, cnt);
-      const int nrv = wmax <= V0 ? V0 : wmax <= V1 ? V1 : wmax <= V2 ? V2 : V3;
+      int nrv = pick_variant(wmax);
       #pragma unroll 1
       // unused slots of the chosen scan variant hold NaN: they lose every max and pass no test
       for (int j = cnt; j < nrv; j++) { dsm[3 * j][tid] = RT_NAN; dsm[3 * j + 1][tid] = RT_NAN; dsm[3 * j + 2][tid] = RT_NAN; }
-      n_live_sum += cnt; n_pass_sum++;
-      // ---- spheres ---------------------------------------------------------------
-      for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
-        const int n = min(RT_CHUNK, sc.n_spheres - cs);
-        if (nrv == V0) scan_chunk<V0>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-        else if (nrv == V1) scan_chunk<V1>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-        else if (nrv == V2) scan_chunk<V2>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-        else scan_chunk<V3>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-      }
+      n_pass_sum++;
+      // A shadow ray is done at its first hit (find_nearest_object's result is only compared with
+      // NULL, C/raycast.c:401-402) and the order of the tests is free, so: planes first (few, and
+      // every one cuts half of space), spheres by descending radius (host order), and whenever
+      // the largest number of rays still alive in the warp fits a smaller scan variant the
+      // survivors are packed to the front of the slot array and the scan continues with it.
+      auto repack = [&]() {
+        const int wlive = __reduce_max_sync(vmask, __popc(alive));
+        const int nv = pick_variant(wlive);
+        if (nv >= nrv) return;                                 // warp-uniform
+        const int sh = r_on ? 1 : 0;
+        int k = 0;
+        unsigned long long nl = 0;
+        for (unsigned m = alive; m; m &= m - 1) {
+          const int j = __ffs(m) - 1;
+          if (k != j) { dsm[3 * k][tid] = dsm[3 * j][tid]; dsm[3 * k + 1][tid] = dsm[3 * j + 1][tid]; dsm[3 * k + 2][tid] = dsm[3 * j + 2][tid]; }
+          if (j >= sh) nl |= ((lmap >> (4 * (j - sh))) & 15ull) << (4 * (k - sh));
+          k++;
+        }
+        lmap = nl;
+        alive = (1u << k) - 1u;
+        for (int j = k; j < nv; j++) { dsm[3 * j][tid] = RT_NAN; dsm[3 * j + 1][tid] = RT_NAN; dsm[3 * j + 2][tid] = RT_NAN; }
+        nrv = nv;
+      };
       // ---- planes ----------------------------------------------------------------
       // t = (-1*num)/den as the reference computes it (C/raycast.c:545-562): den == 0 or
       // t < 0 is a miss, and a hit counts only with 0 < t < inf (:476).
+      d_pln += (unsigned)__popc(alive) * (unsigned)sc.n_planes;
       for (int p = 0; p < sc.n_planes; p++) {
         const int idx = sc.pln_idx[p];
         if (idx == obj) continue;                              // C/raycast.c:450
@@ -530,13 +576,23 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
           }
         }
       }
+      if (sc.n_planes) repack();
+      // ---- spheres ---------------------------------------------------------------
+      for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
+        const int n = min(RT_CHUNK, sc.n_spheres - cs);
+        d_sph += (unsigned)__popc(alive) * (unsigned)n;
+        d_slots += (unsigned)nrv * (unsigned)n;
+        scan_spheres_v<NR, VMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        if (nrv > VMIN) repack();
+      }
       // ---- quadrics --------------------------------------------------------------
+      if constexpr (QUADS)
       for (int cs = 0; cs < sc.n_quadrics; cs += RT_CHUNK) {
         const int n = min(RT_CHUNK, sc.n_quadrics - cs);
-        if (nrv == V0) scan_quadrics<V0>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-        else if (nrv == V1) scan_quadrics<V1>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-        else if (nrv == V2) scan_quadrics<V2>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-        else scan_quadrics<V3>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        d_quad += (unsigned)__popc(alive) * (unsigned)n;
+        d_slots += (unsigned)nrv * (unsigned)n;
+        scan_quadrics_v<NR, VMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+        if (nrv > VMIN) repack();
       }
       // ---- Phong for the lights of this pass that stayed unoccluded, in light order
       for (unsigned m = alive & ~(r_on ? 1u : 0u); m; m &= m - 1) {
@@ -593,9 +649,9 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
                  hit_class(sc, P2, N2, best_idx, level + 1 < 6, NR));
     }
   }
-  unsigned v[7] = {n_refl, n_lit, n_hp, n_pass_sum, n_live_sum, n_ls, n_cand};
+  unsigned v[10] = {n_refl, n_lit, n_hp, n_pass_sum, d_sph, n_ls, n_cand, d_pln, d_quad, d_slots};
   #pragma unroll
-  for (int k = 0; k < 7; k++) {
+  for (int k = 0; k < 10; k++) {
     #pragma unroll
     for (int off = 16; off; off >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
   }
@@ -610,11 +666,10 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
       if (np) atomicAdd(&counters[CT_PLN_O], v[3] * np);
       if (nq) atomicAdd(&counters[CT_QUAD_O], v[3] * nq);
     }
-    if (v[4]) {
-      if (ns) atomicAdd(&counters[CT_SPH_D], v[4] * ns);
-      if (np) atomicAdd(&counters[CT_PLN_D], v[4] * np);
-      if (nq) atomicAdd(&counters[CT_QUAD_D], v[4] * nq);
-    }
+    if (v[4]) atomicAdd(&counters[CT_SPH_D], (u64)v[4]);
+    if (v[7]) atomicAdd(&counters[CT_PLN_D], (u64)v[7]);
+    if (v[8]) atomicAdd(&counters[CT_QUAD_D], (u64)v[8]);
+    if (v[9]) atomicAdd(&counters[CT_SLOTS], (u64)v[9]);
     if (v[5]) atomicAdd(&counters[CT_LIGHT_SAMPLES], (u64)v[5]);
     if (v[6]) atomicAdd(&counters[CT_CANDIDATES], (u64)v[6]);
   }

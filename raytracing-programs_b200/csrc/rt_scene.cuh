@@ -46,5 +46,5 @@ struct HitQueue {
 enum {
   CT_RAYS_REFLECTION = 0, CT_RAYS_SHADOW, CT_HIT_POINTS, CT_PRIMARY_HITS,
   CT_SPH_O, CT_SPH_D, CT_PLN_O, CT_PLN_D, CT_QUAD_O, CT_QUAD_D,
-  CT_LIGHT_SAMPLES, CT_CANDIDATES, CT_COUNT
+  CT_LIGHT_SAMPLES, CT_CANDIDATES, CT_SLOTS, CT_COUNT
 };
