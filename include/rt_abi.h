@@ -115,6 +115,13 @@ void rt_shutdown(void);
 const char *rt_last_error(void);
 int rt_abi_version(void);
 
+/* Acceleration of the nearest-hit search, read by the next rt_scene_upload.
+ * 0 (default): every ray tests every shape, as C/raycast.c:449 does.  1: the sphere part of shadow
+ * queries goes through a per-light cube-map "light buffer" built at upload time; the lists are
+ * conservative with respect to the reference's float arithmetic, so the image is the same, byte
+ * for byte.  Env RT_ACCEL=0/1 overrides. */
+int rt_set_accel(int mode);
+
 /* Flatten to type-sorted SoA (+ original index) and upload to every device in use.
  * Takes the place of the list->VLA copy at C/raycast.c:87-107. The scene is copied;
  * the caller keeps ownership of its arrays. */

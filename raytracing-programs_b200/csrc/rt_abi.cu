@@ -13,6 +13,8 @@
 #include <string.h>
 #include <sys/time.h>
 #include <algorithm>
+#include <thread>
+#include <utility>
 #include <vector>
 
 #include "rt_abi.h"
@@ -80,6 +82,7 @@ DeviceCtx g_dev[RT_MAX_GPUS];
 int g_ndev = 0;
 bool g_have_scene = false;
 int g_n_lights = 0, g_n_shapes = 0;
+int g_accel = 0;   // rt_set_accel / RT_ACCEL: light buffer for the sphere part of shadow queries
 
 // ---- NCCL through dlopen ---------------------------------------------------------
 struct NcclApi {
@@ -162,12 +165,189 @@ void free_device(DeviceCtx &d) {
 void warm_modules() {
   cudaFuncAttributes fa;
   cudaFuncGetAttributes(&fa, k_primary); cudaFuncGetAttributes(&fa, k_finalize); cudaFuncGetAttributes(&fa, k_assemble);
-  cudaFuncGetAttributes(&fa, k_shade<1, true>); cudaFuncGetAttributes(&fa, k_shade<2, true>); cudaFuncGetAttributes(&fa, k_shade<4, true>);
-  cudaFuncGetAttributes(&fa, k_shade<8, true>); cudaFuncGetAttributes(&fa, k_shade<16, true>);
-  cudaFuncGetAttributes(&fa, k_shade<1, false>); cudaFuncGetAttributes(&fa, k_shade<2, false>); cudaFuncGetAttributes(&fa, k_shade<4, false>);
-  cudaFuncGetAttributes(&fa, k_shade<8, false>); cudaFuncGetAttributes(&fa, k_shade<16, false>);
+  // (the k_shade instantiations are loaded by shade_fn() at their first use: 20 of them, one is used per scene)
   cudaFuncGetAttributes(&fa, k_p3_count); cudaFuncGetAttributes(&fa, k_p3_scan); cudaFuncGetAttributes(&fa, k_p3_emit);
   cudaGetLastError();
+}
+
+// ---- light buffer ----------------------------------------------
+// Exact acceleration of the sphere part of shadow queries.  A shadow ray towards light L from P lies
+// on the line through L with direction u = (P - L)/|P - L| (the reference sets no t_max, so the part
+// beyond the light counts too: direction -u).  The reference can report a hit on sphere (C, r) only
+// if its float discriminant is >= 0, which by the reject-filter contract needs the line
+// to pass within r_eff = sqrt(r^2 + 2^-17 (T + r^2)) of C, T = |P - C|^2; for |P - L| <= Dcap,
+// T <= (Dcap + |C - L|)^2.  So per light, per distance level (Dcap = 2, 8, 32 x the light's scene
+// radius) and per cube-map cell the list holds every sphere whose cone of half-angle
+// asin(r_eff / |C - L|) around +-(C - L), widened by the cell's own angular radius and a 3e-4 rad
+// margin (float rounding of the direction and of the cell lookup is ~1e-7), meets the cell.
+// Hit points farther than the last level, and degenerate lights, fall back to testing every sphere.
+struct LightBuffer {
+  std::vector<unsigned> start;
+  std::vector<int> items;
+  std::vector<float4> caps;
+};
+
+void lb_dir(int face, double s, double t, double *o) {
+  const double sg = (face & 1) ? -1.0 : 1.0;
+  if (face < 2) { o[0] = sg; o[1] = s; o[2] = t; }
+  else if (face < 4) { o[0] = s; o[1] = sg; o[2] = t; }
+  else { o[0] = s; o[1] = t; o[2] = sg; }
+  const double n = sqrt(o[0] * o[0] + o[1] * o[1] + o[2] * o[2]);
+  o[0] /= n; o[1] /= n; o[2] /= n;
+}
+
+// Bounding-sphere hierarchy over sphere slots [0, n): median split along the widest axis of the centres,
+// leaves of <= 4 spheres.  Node sphere: centre of the members' bounding box, radius max(|C - c| + |r|),
+// computed in double and rounded up.  Returns false (no hierarchy) on non-finite geometry or depth > 28.
+struct SphereBvh {
+  std::vector<float4> node;
+  std::vector<int2> kids;
+  std::vector<int> items;
+};
+
+bool bvh_build_rec(const std::vector<float4> &sph, std::vector<int> &ids, int lo, int hi, int depth, SphereBvh &out, int *self) {
+  if (depth > 28) return false;
+  double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+  for (int k = lo; k < hi; k++) {
+    const float4 &q = sph[ids[k]];
+    const double c[3] = {q.x, q.y, q.z}, r = fabs((double)q.w);
+    if (!std::isfinite(c[0]) || !std::isfinite(c[1]) || !std::isfinite(c[2]) || !std::isfinite(r)) return false;
+    for (int a = 0; a < 3; a++) { mn[a] = std::min(mn[a], c[a] - r); mx[a] = std::max(mx[a], c[a] + r); }
+  }
+  const double cc[3] = {0.5 * (mn[0] + mx[0]), 0.5 * (mn[1] + mx[1]), 0.5 * (mn[2] + mx[2])};
+  const float cf[3] = {(float)cc[0], (float)cc[1], (float)cc[2]};
+  double R = 0;
+  for (int k = lo; k < hi; k++) {
+    const float4 &q = sph[ids[k]];
+    const double dx = q.x - (double)cf[0], dy = q.y - (double)cf[1], dz = q.z - (double)cf[2];
+    R = std::max(R, sqrt(dx * dx + dy * dy + dz * dz) + fabs((double)q.w));
+  }
+  const float Rf = (float)(R * (1.0 + 1e-6)) + 1e-30f;
+  if (!std::isfinite(Rf)) return false;
+  const int me = (int)out.node.size();
+  *self = me;
+  out.node.push_back(make_float4(cf[0], cf[1], cf[2], Rf));
+  out.kids.push_back(make_int2(0, 0));
+  if (hi - lo <= 4) {
+    out.kids[me] = make_int2(-((int)out.items.size() + 1), hi - lo);
+    for (int k = lo; k < hi; k++) out.items.push_back(ids[k]);
+    return true;
+  }
+  int axis = 0;
+  double ext = -1;
+  for (int a = 0; a < 3; a++) {
+    double cmn = 1e300, cmx = -1e300;
+    for (int k = lo; k < hi; k++) { const float4 &q = sph[ids[k]]; const double v = a == 0 ? q.x : a == 1 ? q.y : q.z; cmn = std::min(cmn, v); cmx = std::max(cmx, v); }
+    if (cmx - cmn > ext) { ext = cmx - cmn; axis = a; }
+  }
+  const int mid = (lo + hi) / 2;
+  std::nth_element(ids.begin() + lo, ids.begin() + mid, ids.begin() + hi, [&](int x, int y) {
+    const float4 &a = sph[x], &b = sph[y];
+    return (axis == 0 ? a.x : axis == 1 ? a.y : a.z) < (axis == 0 ? b.x : axis == 1 ? b.y : b.z);
+  });
+  int l = 0, r = 0;
+  if (!bvh_build_rec(sph, ids, lo, mid, depth + 1, out, &l)) return false;
+  if (!bvh_build_rec(sph, ids, mid, hi, depth + 1, out, &r)) return false;
+  out.kids[me] = make_int2(l, r);
+  return true;
+}
+
+bool build_sphere_bvh(const std::vector<float4> &sph, int n_sph, SphereBvh &out) {
+  std::vector<int> ids(n_sph);
+  for (int i = 0; i < n_sph; i++) ids[i] = i;
+  int root = 0;
+  return n_sph > 0 && bvh_build_rec(sph, ids, 0, n_sph, 0, out, &root);
+}
+
+bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, int n_sph, LightBuffer &lb) {
+  const int R = RT_LB_RES, CELLS = 6 * R * R, nl = scene->num_lights;
+  std::vector<double> cb(3 * (size_t)CELLS), cbeta(CELLS);
+  for (int face = 0; face < 6; face++)
+    for (int j = 0; j < R; j++)
+      for (int i = 0; i < R; i++) {
+        const int c = (face * R + j) * R + i;
+        const double s0 = -1.0 + 2.0 * i / R, s1 = -1.0 + 2.0 * (i + 1) / R, t0 = -1.0 + 2.0 * j / R, t1 = -1.0 + 2.0 * (j + 1) / R;
+        double b[3], q[3], beta = 0;
+        lb_dir(face, 0.5 * (s0 + s1), 0.5 * (t0 + t1), b);
+        const double cs[4][2] = {{s0, t0}, {s1, t0}, {s0, t1}, {s1, t1}};
+        for (auto &k : cs) {
+          lb_dir(face, k[0], k[1], q);
+          double d = b[0] * q[0] + b[1] * q[1] + b[2] * q[2];
+          d = d > 1 ? 1 : d < -1 ? -1 : d;
+          beta = std::max(beta, acos(d));
+        }
+        cb[3 * c] = b[0]; cb[3 * c + 1] = b[1]; cb[3 * c + 2] = b[2]; cbeta[c] = beta;
+      }
+  lb.caps.assign((size_t)nl + 1, make_float4(-1.f, -1.f, -1.f, 0.f));
+  std::vector<std::vector<unsigned>> cnt((size_t)nl * RT_LB_LEVELS);           // per (light, level): CSR counts
+  std::vector<std::vector<std::pair<int, int>>> pairs((size_t)nl * RT_LB_LEVELS);   // (cell, sphere)
+  auto work = [&](int l) {
+    const rt_light &t = scene->lights[l];
+    const double L[3] = {t.position[0], t.position[1], t.position[2]};
+    if (!std::isfinite(L[0]) || !std::isfinite(L[1]) || !std::isfinite(L[2])) return;
+    double Rl = 0;
+    for (int s = 0; s < n_sph; s++) {
+      const double dx = sph[s].x - L[0], dy = sph[s].y - L[1], dz = sph[s].z - L[2], r = fabs((double)sph[s].w);
+      const double d = sqrt(dx * dx + dy * dy + dz * dz) + r;
+      if (std::isfinite(d)) Rl = std::max(Rl, d);
+    }
+    if (!(Rl > 0) || !(Rl < 1e15)) return;
+    const double mult[RT_LB_LEVELS] = {2.0, 8.0, 32.0};
+    float capf[RT_LB_LEVELS];
+    for (int lv = 0; lv < RT_LB_LEVELS; lv++) {
+      const double Dcap = Rl * mult[lv];
+      capf[lv] = (float)((Dcap * (1.0 - 1e-3)) * (Dcap * (1.0 - 1e-3)));
+      auto &pv = pairs[(size_t)l * RT_LB_LEVELS + lv];
+      for (int s = 0; s < n_sph; s++) {
+        const double dx = sph[s].x - L[0], dy = sph[s].y - L[1], dz = sph[s].z - L[2], r = fabs((double)sph[s].w);
+        const double dist = sqrt(dx * dx + dy * dy + dz * dz);
+        const double Tcap = (Dcap + dist) * (Dcap + dist);
+        const double reff = sqrt(r * r + ldexp(1.0, -17) * (Tcap + r * r)) + ldexp(8.0, -24) * sqrt(Tcap);
+        const bool all = !(dist > reff * (1.0 + 1e-6)) || !std::isfinite(reff);
+        double a[3] = {0, 0, 0}, theta = 4.0;
+        if (!all) { a[0] = dx / dist; a[1] = dy / dist; a[2] = dz / dist; theta = asin(std::min(1.0, reff / dist)) + 3e-4; }
+        for (int face = 0; face < 6; face++) {
+          if (!all) {   // whole face out of reach? (a cube face spans acos(1/sqrt 3) = 0.9554 rad around its axis)
+            const double ax = fabs(a[face >> 1]), reach = theta + 0.9555;
+            if (reach < 1.5707 && ax < cos(reach)) continue;
+          }
+          for (int k = 0; k < R * R; k++) {
+            const int c = face * R * R + k;
+            bool in = all;
+            if (!in) {
+              const double ang = theta + cbeta[c];
+              if (ang >= 3.14159) in = true;
+              else { const double dd = cb[3 * c] * a[0] + cb[3 * c + 1] * a[1] + cb[3 * c + 2] * a[2]; in = fabs(dd) >= cos(ang) || cos(ang) <= 0; }
+            }
+            if (in) pv.push_back(std::make_pair(c, s));
+          }
+        }
+      }
+    }
+    lb.caps[l] = make_float4(capf[0], capf[1], capf[2], 0.f);
+  };
+  {
+    std::vector<std::thread> th;
+    for (int l = 0; l < nl; l++) th.emplace_back(work, l);
+    for (auto &x : th) x.join();
+  }
+  size_t total = 0;
+  for (auto &pv : pairs) total += pv.size();
+  if (total > ((size_t)64 << 20)) return false;   // degenerate scene (NaN geometry everywhere): no light buffer
+  lb.start.assign((size_t)nl * RT_LB_LEVELS * CELLS + 1, 0u);
+  lb.items.resize(total + 1);
+  size_t base = 0;
+  for (size_t g = 0; g < pairs.size(); g++) {
+    std::vector<unsigned> c((size_t)CELLS + 1, 0u);
+    for (auto &pr : pairs[g]) c[pr.first + 1]++;
+    for (int k = 0; k < CELLS; k++) c[k + 1] += c[k];
+    for (int k = 0; k < CELLS; k++) lb.start[g * CELLS + k] = (unsigned)(base + c[k]);
+    std::vector<unsigned> fill(c.begin(), c.end() - 1);
+    for (auto &pr : pairs[g]) lb.items[base + fill[pr.first]++] = pr.second;
+    base += pairs[g].size();
+  }
+  lb.start[(size_t)nl * RT_LB_LEVELS * CELLS] = (unsigned)base;
+  return true;
 }
 
 }  // namespace
@@ -176,6 +356,11 @@ void warm_modules() {
 extern "C" {
 
 int rt_abi_version(void) { return RT_ABI_VERSION; }
+int rt_set_accel(int mode) {
+  if (mode != 0 && mode != 1) return set_err(RT_ERR_ARG, "rt_set_accel: mode must be 0 or 1");
+  g_accel = mode;
+  return RT_OK;
+}
 const char *rt_last_error(void) { return g_err; }
 int rt_device_count(void) { return g_ndev; }
 int rt_band_height(void) { return band_rows(); }
@@ -348,16 +533,27 @@ int rt_scene_upload(const rt_scene *scene) {
     sph_idx.push_back(-2);
   }
   const int n_sph_real = (int)slot_count_spheres;
+  // light buffer (opt-in: rt_set_accel(1) or RT_ACCEL=1)
+  LightBuffer lb;
+  const char *env_accel = getenv("RT_ACCEL");
+  const bool want_accel = env_accel ? atoi(env_accel) != 0 : g_accel != 0;
+  SphereBvh bvh;
+  const bool have_lb = want_accel && nl > 0 && n_sph_real > 0 && build_sphere_bvh(sph, n_sph_real, bvh) &&
+                       build_light_buffer(scene, sph, n_sph_real, lb);
   // one blob, 256-byte aligned sections
   struct Sec { const void *src; size_t bytes; size_t off; };
-  Sec secs[13] = {
+  Sec secs[19] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
       {quad_idx.data(), quad_idx.size() * 4, 0}, {mat.data(), mat.size() * 16, 0},
       {slot.data(), slot.size() * 8, 0},       {lights.data(), lights.size() * 16, 0},
       {sph_hot.data(), sph_hot.size() * 16, 0}, {quad_hot.data(), quad_hot.size() * 16, 0},
-      {quad_prim.data(), quad_prim.size() * 16, 0}};
+      {quad_prim.data(), quad_prim.size() * 16, 0},
+      {lb.start.data(), have_lb ? lb.start.size() * 4 : 0, 0}, {lb.items.data(), have_lb ? lb.items.size() * 4 : 0, 0},
+      {lb.caps.data(), have_lb ? lb.caps.size() * 16 : 0, 0},
+      {bvh.node.data(), have_lb ? bvh.node.size() * 16 : 0, 0}, {bvh.kids.data(), have_lb ? bvh.kids.size() * 8 : 0, 0},
+      {bvh.items.data(), have_lb ? bvh.items.size() * 4 : 0, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -384,6 +580,12 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.slot = (const int2 *)(b + secs[8].off); sc.lights = (const float4 *)(b + secs[9].off);
     sc.sph_hot = (const float4 *)(b + secs[10].off);
     sc.quad_hot = (const float4 *)(b + secs[11].off); sc.quad_prim = (const float4 *)(b + secs[12].off);
+    sc.lb_start = have_lb ? (const unsigned *)(b + secs[13].off) : nullptr;
+    sc.lb_items = have_lb ? (const int *)(b + secs[14].off) : nullptr;
+    sc.lb_caps = have_lb ? (const float4 *)(b + secs[15].off) : nullptr;
+    sc.bvh_node = have_lb ? (const float4 *)(b + secs[16].off) : nullptr;
+    sc.bvh_kids = have_lb ? (const int2 *)(b + secs[17].off) : nullptr;
+    sc.bvh_items = have_lb ? (const int *)(b + secs[18].off) : nullptr;
   }
   g_have_scene = true;
   g_n_lights = nl;
@@ -395,19 +597,27 @@ int rt_scene_upload(const rt_scene *scene) {
 
 namespace {
 
+typedef void (*shade_fn_t)(DevScene, int, HitQueue, HitQueue, float4 *, float4 *, unsigned long long *);
+
+// The k_shade instantiation for this scene: LB lights per pass, with / without the quadric sections,
+// with / without the light buffer.
+template <int LB>
+shade_fn_t shade_fn(const DeviceCtx &d) {
+  const bool q = d.sc.n_quadrics > 0, a = d.sc.lb_start != nullptr;
+  return q ? (a ? k_shade<LB, true, true> : k_shade<LB, true, false>) : (a ? k_shade<LB, false, true> : k_shade<LB, false, false>);
+}
+
 template <int LB>
 int shade_grid(DeviceCtx &d) {
   int per_sm = 0;
-  if (d.sc.n_quadrics > 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_shade<LB, true>, 128, 0);
-  else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_shade<LB, false>, 128, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, shade_fn<LB>(d), 128, 0);
   if (per_sm < 1) per_sm = 1;
   return per_sm * d.sm_count;
 }
 
 template <int LB>
 void launch_shade(DeviceCtx &d, int grid, int level, HitQueue qin, HitQueue qout) {
-  if (d.sc.n_quadrics > 0) k_shade<LB, true><<<grid, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters);
-  else k_shade<LB, false><<<grid, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters);
+  shade_fn<LB>(d)<<<grid, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters);
 }
 
 int pick_lb(int n_lights) {

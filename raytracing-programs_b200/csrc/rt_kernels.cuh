@@ -408,6 +408,90 @@ RT_DEV void scan_quadrics(const float (*dsm)[128], unsigned char (*cand)[128], c
   }
 }
 
+// One shadow ray (origin P, direction dj) against sphere slot ss: does the reference report a hit with
+// 0 < t < inf?  Same decision chain as the resolve stage of scan_chunk: conservative filter, sign
+// analysis where the margins allow it, the reference's literal root otherwise.
+RT_DEV bool shadow_hits_sphere(const DevScene &sc, const v3 P, const v3 dj, const int ss, unsigned &n_cand) {
+  const float4 hh = sc.sph_hot[ss];
+  const float xs = P.x - hh.x, ys = P.y - hh.y, zs = P.z - hh.z;
+  const float Ts = __fmaf_rn(zs, zs, __fmaf_rn(ys, ys, xs * xs));
+  const float cp = Ts - hh.w, marg = RT_FILTER_EPS * (Ts + hh.w);
+  const float lo = cp - marg, hi = cp + marg;
+  const float e = __fmaf_rn(dj.z, zs, __fmaf_rn(dj.y, ys, dj.x * xs));
+  const float e2 = e * e;
+  if (!(e2 >= lo)) return false;
+  const float guard = 1.52587890625e-05f * e2;
+  const bool inside = cp <= -(marg + guard);
+  const bool outside = (cp >= marg + guard) && (e2 >= hi);
+  if (inside || outside) return inside || e < 0.0f;
+  n_cand++;
+  float t;
+  return sphere_t_literal(P, dj, sc.sph[ss], t) && (t > 0.0f) && (t < RT_INF);
+}
+
+// One reflection ray against sphere slot ss (nearest hit): the decision chain of scan_chunk's resolve stage.
+RT_DEV void refl_test_sphere(const DevScene &sc, const v3 P, const v3 dj, const int ss, float &best_t, int &best_idx,
+                             unsigned &n_cand) {
+  const float4 hh = sc.sph_hot[ss];
+  const float xs = P.x - hh.x, ys = P.y - hh.y, zs = P.z - hh.z;
+  const float Ts = __fmaf_rn(zs, zs, __fmaf_rn(ys, ys, xs * xs));
+  const float cp = Ts - hh.w, marg = RT_FILTER_EPS * (Ts + hh.w);
+  const float lo = cp - marg, hi = cp + marg;
+  const float e = __fmaf_rn(dj.z, zs, __fmaf_rn(dj.y, ys, dj.x * xs));
+  const float e2 = e * e;
+  if (!(e2 >= lo)) return;
+  const float guard = 1.52587890625e-05f * e2;
+  const bool outside = (cp >= marg + guard) && (e2 >= hi);
+  if (outside && e > 0.0f) return;                             // both roots behind the origin
+  n_cand++;
+  float t;
+  const int idx = sc.sph_idx[ss];
+  if (sphere_t_literal(P, dj, sc.sph[ss], t) && better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
+}
+
+// Traversal of the bounding-sphere hierarchy for one ray.  A node is entered unless the ray certainly
+// misses every member in the REFERENCE's arithmetic: the reference can accept sphere (C, r) only if the
+// line passes within r (1 + 2^-17) + 2^-8 sqrt(T) of C (reject-filter contract, T = |P - C|^2 <=
+// (|P - Cn| + Rn)^2 for a member of node (Cn, Rn)), so the node sphere is inflated by that much plus the
+// float slack of this test itself; nodes wholly behind the origin (with the larger 2^-6 margin the
+// "both roots negative" argument needs) and, for nearest hit, wholly beyond the best t so far are skipped.
+// ANY = true: shadow query, returns at the first hit.  Returns whether anything was hit (ANY) / unused.
+template <bool ANY>
+RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj, float &best_t, int &best_idx,
+                      unsigned &n_cand, unsigned &n_tests) {
+  int stack[32];
+  int sp = 0;
+  stack[sp++] = 0;
+  while (sp > 0) {
+    const int k = stack[--sp];
+    const float4 nd = sc.bvh_node[k];
+    const float wx = P.x - nd.x, wy = P.y - nd.y, wz = P.z - nd.z;
+    const float Tn = __fmaf_rn(wz, wz, __fmaf_rn(wy, wy, wx * wx));
+    const float en = __fmaf_rn(d.z, wz, __fmaf_rn(d.y, wy, d.x * wx));
+    const float reach = sqrtf(Tn) + nd.w;                      // >= sqrt(T) of every member
+    const float rinf = __fmaf_rn(nd.w, 1.0001f, 0.005859375f * reach);   // Rn (1 + 1e-4) + (2^-8 + 2^-9) reach
+    // line misses the inflated node?  (Tn - en^2 is the squared distance, float slack 1e-5 Tn)
+    if (!(Tn - en * en <= __fmaf_rn(rinf, rinf, 1e-5f * Tn))) continue;
+    const float rbehind = __fmaf_rn(nd.w, 1.001f, 0.015625f * reach);     // Rn (1 + 1e-3) + 2^-6 reach
+    if (en > rbehind) continue;                                // whole node behind the origin
+    if (!ANY && (-en - rinf) > __fmaf_rn(best_t, 1.001f, 4e-3f * reach)) continue;   // whole node beyond the best hit
+    const int2 kid = sc.bvh_kids[k];
+    if (kid.x >= 0) {
+      stack[sp++] = kid.y; stack[sp++] = kid.x;                // depth <= 28 (host), one net entry per level
+    } else {
+      const int first = -kid.x - 1;
+      for (int i = 0; i < kid.y; i++) {
+        const int ss = sc.bvh_items[first + i];
+        n_tests++;
+        if (sc.sph_idx[ss] == obj) continue;                   // C/raycast.c:450
+        if (ANY) { if (shadow_hits_sphere(sc, P, d, ss, n_cand)) return true; }
+        else refl_test_sphere(sc, P, d, ss, best_t, best_idx, n_cand);
+      }
+    }
+  }
+  return false;
+}
+
 // Scan variants: the bundle scans are compiled for NR, NR-2, NR-4, ... >= 3 ray slots; a warp runs
 // the smallest one that holds the largest number of rays any of its hit points still has alive.
 template <int NRV, int NRMIN>
@@ -431,7 +515,9 @@ RT_DEV void scan_quadrics_v(const int nrv, const float (*dsm)[128], unsigned cha
 
 // QUADS = false: compiled without the quadric sections for scenes that have none (half the code:
 // the instruction cache is the scarce resource of this kernel).
-template <int LB, bool QUADS>
+// ACCEL = true: the sphere part of every shadow query goes through the light buffer (rt_scene.cuh)
+// instead of the bundle scan; the reflection ray still scans every sphere.
+template <int LB, bool QUADS, bool ACCEL>
 __global__ void __launch_bounds__(128, RT_SHADE_MINB)
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
         float4 *__restrict__ c0, unsigned long long *__restrict__ counters) {
@@ -444,7 +530,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
   // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
   // counters are products of these with the scene's primitive counts, formed at the end
   unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_ls = 0, n_cand = 0;
-  unsigned d_sph = 0, d_pln = 0, d_quad = 0, d_slots = 0;   // direction tests executed: live ray slots x primitives scanned with them
+  unsigned d_sph = 0, d_pln = 0, d_quad = 0, d_slots = 0, o_sph = 0;   // direction tests executed: live ray slots x primitives scanned with them
   // Dynamic scheduling: every warp claims 32 consecutive entries of one class list at a time
   // (heaviest class first), so no SM idles while another still holds a backlog, and the hit
   // points a warp shades together need about the same number of ray slots.
@@ -578,12 +664,53 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
       }
       if (sc.n_planes) repack();
       // ---- spheres ---------------------------------------------------------------
-      for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
-        const int n = min(RT_CHUNK, sc.n_spheres - cs);
-        d_sph += (unsigned)__popc(alive) * (unsigned)n;
-        d_slots += (unsigned)nrv * (unsigned)n;
-        scan_spheres_v<NR, VMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-        if (nrv > VMIN) repack();
+      if constexpr (!ACCEL) {
+        o_sph += (unsigned)sc.n_spheres;
+        for (int cs = 0; cs < sc.n_spheres; cs += RT_CHUNK) {
+          const int n = min(RT_CHUNK, sc.n_spheres - cs);
+          d_sph += (unsigned)__popc(alive) * (unsigned)n;
+          d_slots += (unsigned)nrv * (unsigned)n;
+          scan_spheres_v<NR, VMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+          if (nrv > VMIN) repack();
+        }
+      } else {
+        // shadow rays: only the spheres listed in the cell of the light buffer that the direction
+        // from the light to P falls in (level by |P - L|; beyond the last level: every sphere)
+        for (unsigned m = alive & ~(r_on ? 1u : 0u); m; m &= m - 1) {
+          const int j = __ffs(m) - 1;
+          const int l = pass * LB + (int)((lmap >> (4 * (j - (r_on ? 1 : 0)))) & 15ull);
+          const float4 lp = sc.lights[4 * l];
+          const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+          const float wx = lp.x - P.x, wy = lp.y - P.y, wz = lp.z - P.z;
+          const float q = __fmaf_rn(wz, wz, __fmaf_rn(wy, wy, wx * wx));
+          const float4 caps = sc.lb_caps[l];
+          const int lv = q <= caps.x ? 0 : q <= caps.y ? 1 : q <= caps.z ? 2 : -1;
+          const int cell = lb_cell(-dj.x, -dj.y, -dj.z);
+          bool occl = false;
+          if (lv >= 0 && cell >= 0) {
+            const unsigned *st = sc.lb_start + ((size_t)(l * RT_LB_LEVELS + lv) * 6 * RT_LB_RES * RT_LB_RES + cell);
+            const unsigned k1 = st[1];
+            for (unsigned k = st[0]; k < k1 && !occl; k++) {
+              const int ss = sc.lb_items[k];
+              o_sph++; d_sph++;
+              if (sc.sph_idx[ss] != obj) occl = shadow_hits_sphere(sc, P, dj, ss, n_cand);   // C/raycast.c:450
+            }
+          } else {
+            unsigned nt = 0;
+            float bt = RT_INF;
+            int bi = -1;
+            occl = bvh_trace<true>(sc, P, dj, obj, bt, bi, n_cand, nt);
+            o_sph += nt; d_sph += nt;
+          }
+          if (occl) alive &= ~(1u << j);
+        }
+        // reflection ray: nearest hit through the bounding-sphere hierarchy
+        if (r_on) {
+          unsigned nt = 0;
+          bvh_trace<false>(sc, P, rd, obj, best_t, best_idx, n_cand, nt);
+          o_sph += nt; d_sph += nt; d_slots += nt;
+        }
+        repack();
       }
       // ---- quadrics --------------------------------------------------------------
       if constexpr (QUADS)
@@ -649,20 +776,19 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
                  hit_class(sc, P2, N2, best_idx, level + 1 < 6, NR));
     }
   }
-  unsigned v[10] = {n_refl, n_lit, n_hp, n_pass_sum, d_sph, n_ls, n_cand, d_pln, d_quad, d_slots};
+  unsigned v[11] = {n_refl, n_lit, n_hp, n_pass_sum, d_sph, n_ls, n_cand, d_pln, d_quad, d_slots, o_sph};
   #pragma unroll
-  for (int k = 0; k < 10; k++) {
+  for (int k = 0; k < 11; k++) {
     #pragma unroll
     for (int off = 16; off; off >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
   }
   if ((threadIdx.x & 31) == 0) {
     typedef unsigned long long u64;
-    const u64 ns = sc.n_spheres, np = sc.n_planes, nq = sc.n_quadrics;
+    const u64 np = sc.n_planes, nq = sc.n_quadrics;
     if (v[0]) atomicAdd(&counters[CT_RAYS_REFLECTION], (u64)v[0]);
     if (v[1]) atomicAdd(&counters[CT_RAYS_SHADOW], (u64)v[1] * sc.n_lights);
     if (v[2]) atomicAdd(&counters[CT_HIT_POINTS], (u64)v[2]);
     if (v[3]) {
-      if (ns) atomicAdd(&counters[CT_SPH_O], v[3] * ns);
       if (np) atomicAdd(&counters[CT_PLN_O], v[3] * np);
       if (nq) atomicAdd(&counters[CT_QUAD_O], v[3] * nq);
     }
@@ -670,6 +796,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
     if (v[7]) atomicAdd(&counters[CT_PLN_D], (u64)v[7]);
     if (v[8]) atomicAdd(&counters[CT_QUAD_D], (u64)v[8]);
     if (v[9]) atomicAdd(&counters[CT_SLOTS], (u64)v[9]);
+    if (v[10]) atomicAdd(&counters[CT_SPH_O], (u64)v[10]);
     if (v[5]) atomicAdd(&counters[CT_LIGHT_SAMPLES], (u64)v[5]);
     if (v[6]) atomicAdd(&counters[CT_CANDIDATES], (u64)v[6]);
   }

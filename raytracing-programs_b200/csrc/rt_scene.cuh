@@ -23,7 +23,38 @@ struct DevScene {
   const float4 *mat;        // [2*n_shapes] by original index: {Kd.rgb, reflectivity} {Ks.rgb, opacity}
   const int2 *slot;         // [n_shapes] by original index: {type, slot in its type array}
   const float4 *lights;     // [4*n_lights] {pos, type} {color, cos_theta} {radial a0 a1 a2, angular a0} {dir, cull flag}
+  // Light buffer (opt-in exact acceleration of the sphere part of shadow queries):
+  // per light and distance level a cube map of RT_LB_RES^2 cells per face; a cell lists every sphere the
+  // reference could report as hit by a shadow ray whose direction seen from the light falls in the cell.
+  const unsigned *lb_start; // [n_lights * RT_LB_LEVELS * 6 * RT_LB_RES^2 + 1] CSR starts; NULL = no light buffer
+  const int *lb_items;      // sphere slots
+  const float4 *lb_caps;    // [n_lights] squared |P - L| limit of each level {cap0, cap1, cap2, 0}
+  // Bounding-sphere hierarchy over the spheres (same opt-in mode): nearest hit of reflection rays and the
+  // fallback of shadow rays.  Node k: bvh_node[k] = {centre, radius of a sphere holding all member spheres},
+  // bvh_kids[k] = {left, right} child nodes, or for a leaf {-(first + 1), count} into bvh_items (sphere slots).
+  const float4 *bvh_node;
+  const int2 *bvh_kids;
+  const int *bvh_items;
 };
+#define RT_LB_RES 32
+#define RT_LB_LEVELS 3
+
+// Cube-map cell of direction u (any length): face = 2 * major axis + (negative ? 1 : 0), the other two
+// components divided by |major| map [-1, 1] onto RT_LB_RES cells.  Returns -1 for a zero or NaN vector.
+// The host builds the cells with the same mapping in double and a margin that swallows float rounding.
+__host__ __device__ inline int lb_cell(float ux, float uy, float uz) {
+  const float ax = fabsf(ux), ay = fabsf(uy), az = fabsf(uz);
+  float m, s, t;
+  int face;
+  if (ax >= ay && ax >= az) { m = ax; s = uy; t = uz; face = ux < 0.0f ? 1 : 0; }
+  else if (ay >= az) { m = ay; s = ux; t = uz; face = uy < 0.0f ? 3 : 2; }
+  else { m = az; s = ux; t = uy; face = uz < 0.0f ? 5 : 4; }
+  if (!(m > 0.0f) || !(m < 3.0e38f)) return -1;
+  int i = (int)floorf((s / m + 1.0f) * (0.5f * RT_LB_RES)), j = (int)floorf((t / m + 1.0f) * (0.5f * RT_LB_RES));
+  i = i < 0 ? 0 : i > RT_LB_RES - 1 ? RT_LB_RES - 1 : i;
+  j = j < 0 ? 0 : j > RT_LB_RES - 1 ? RT_LB_RES - 1 : j;
+  return (face * RT_LB_RES + j) * RT_LB_RES + i;
+}
 
 // Hit-point queue (one wavefront level): 48 B per entry, structure of float4 arrays, plus one
 // index list per work class.  The producer files every entry under the class of its estimated
