@@ -164,7 +164,7 @@ void free_device(DeviceCtx &d) {
 // CUDA loads kernels lazily: touch every kernel once at init so the first render does not pay for it.
 void warm_modules() {
   cudaFuncAttributes fa;
-  cudaFuncGetAttributes(&fa, k_primary); cudaFuncGetAttributes(&fa, k_finalize); cudaFuncGetAttributes(&fa, k_assemble);
+  cudaFuncGetAttributes(&fa, k_primary<false>); cudaFuncGetAttributes(&fa, k_finalize); cudaFuncGetAttributes(&fa, k_assemble);
   // (the k_shade instantiations are loaded by shade_fn() at their first use: 20 of them, one is used per scene)
   cudaFuncGetAttributes(&fa, k_p3_count); cudaFuncGetAttributes(&fa, k_p3_scan); cudaFuncGetAttributes(&fa, k_p3_emit);
   cudaGetLastError();
@@ -248,7 +248,8 @@ bool bvh_build_rec(const std::vector<float4> &sph, std::vector<int> &ids, int lo
   int l = 0, r = 0;
   if (!bvh_build_rec(sph, ids, lo, mid, depth + 1, out, &l)) return false;
   if (!bvh_build_rec(sph, ids, mid, hi, depth + 1, out, &r)) return false;
-  out.kids[me] = make_int2(l, r);
+  if (r >= (1 << 28)) return false;
+  out.kids[me] = make_int2(l, r | (axis << 28));   // left = lower half along `axis`
   return true;
 }
 
@@ -484,6 +485,21 @@ int rt_scene_upload(const rt_scene *scene) {
     return (rx == rx ? rx : -INFINITY) > (ry == ry ? ry : -INFINITY);   // NaN radii last
   });
   if (getenv("RT_NO_SORT")) std::sort(sphere_order.begin(), sphere_order.end());
+  // accel mode: leaf order of the bounding-sphere hierarchy instead, so a leaf is a run of consecutive slots
+  const char *env_accel = getenv("RT_ACCEL");
+  const bool want_accel = env_accel ? atoi(env_accel) != 0 : g_accel != 0;
+  SphereBvh bvh;
+  bool have_bvh = false;
+  if (want_accel && !sphere_order.empty()) {
+    std::vector<float4> tmp;
+    for (int i : sphere_order) { const rt_shape &s = scene->shapes[i]; tmp.push_back(make_float4(s.position[0], s.position[1], s.position[2], s.params[0])); }
+    have_bvh = build_sphere_bvh(tmp, (int)tmp.size(), bvh);
+    if (have_bvh) {
+      std::vector<int> reordered;
+      for (int k : bvh.items) reordered.push_back(sphere_order[k]);
+      sphere_order.swap(reordered);
+    }
+  }
   for (int i : sphere_order) {
     const rt_shape &s = scene->shapes[i];
     slot[i] = make_int2(0, (int)sph.size());
@@ -535,14 +551,10 @@ int rt_scene_upload(const rt_scene *scene) {
   const int n_sph_real = (int)slot_count_spheres;
   // light buffer (opt-in: rt_set_accel(1) or RT_ACCEL=1)
   LightBuffer lb;
-  const char *env_accel = getenv("RT_ACCEL");
-  const bool want_accel = env_accel ? atoi(env_accel) != 0 : g_accel != 0;
-  SphereBvh bvh;
-  const bool have_lb = want_accel && nl > 0 && n_sph_real > 0 && build_sphere_bvh(sph, n_sph_real, bvh) &&
-                       build_light_buffer(scene, sph, n_sph_real, lb);
+  const bool have_lb = have_bvh && nl > 0 && n_sph_real > 0 && build_light_buffer(scene, sph, n_sph_real, lb);
   // one blob, 256-byte aligned sections
   struct Sec { const void *src; size_t bytes; size_t off; };
-  Sec secs[19] = {
+  Sec secs[18] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
@@ -552,8 +564,7 @@ int rt_scene_upload(const rt_scene *scene) {
       {quad_prim.data(), quad_prim.size() * 16, 0},
       {lb.start.data(), have_lb ? lb.start.size() * 4 : 0, 0}, {lb.items.data(), have_lb ? lb.items.size() * 4 : 0, 0},
       {lb.caps.data(), have_lb ? lb.caps.size() * 16 : 0, 0},
-      {bvh.node.data(), have_lb ? bvh.node.size() * 16 : 0, 0}, {bvh.kids.data(), have_lb ? bvh.kids.size() * 8 : 0, 0},
-      {bvh.items.data(), have_lb ? bvh.items.size() * 4 : 0, 0}};
+      {bvh.node.data(), have_lb ? bvh.node.size() * 16 : 0, 0}, {bvh.kids.data(), have_lb ? bvh.kids.size() * 8 : 0, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -585,7 +596,6 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.lb_caps = have_lb ? (const float4 *)(b + secs[15].off) : nullptr;
     sc.bvh_node = have_lb ? (const float4 *)(b + secs[16].off) : nullptr;
     sc.bvh_kids = have_lb ? (const int2 *)(b + secs[17].off) : nullptr;
-    sc.bvh_items = have_lb ? (const int *)(b + secs[18].off) : nullptr;
   }
   g_have_scene = true;
   g_n_lights = nl;
@@ -661,7 +671,8 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
   }
   const int lb = pick_lb(d.sc.n_lights);
   int per_sm = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_primary, 256, 0);
+  if (d.sc.bvh_node) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_primary<true>, 256, 0);
+  else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_primary<false>, 256, 0);
   d.grid_primary = (per_sm > 0 ? per_sm : 1) * d.sm_count;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_finalize, 256, 0);
   d.grid_fin = (per_sm > 0 ? per_sm : 1) * d.sm_count;
@@ -690,9 +701,11 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     tg.n_px = (int)((px_total - first) < (long long)tile ? (px_total - first) : (long long)tile);
     CK(cudaMemsetAsync(d.qcount, 0, 8 * RT_CTL_STRIDE * sizeof(int), d.stream));
     HitQueue q0 = q[0]; q0.ctl = d.qcount;
-    int gp = (tg.n_px + 256 * RT_PRIM_PX - 1) / (256 * RT_PRIM_PX); if (gp > d.grid_primary) gp = d.grid_primary;
+    const int ppx = d.sc.bvh_node ? 1 : RT_PRIM_PX_BRUTE;
+    int gp = (tg.n_px + 256 * ppx - 1) / (256 * ppx); if (gp > d.grid_primary) gp = d.grid_primary;
     if ((mr = mark(d, 'p')) != RT_OK) return mr;
-    k_primary<<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, lb + 1, d.counters);
+    if (d.sc.bvh_node) k_primary<true><<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, lb + 1, d.counters);
+    else k_primary<false><<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, lb + 1, d.counters);
     plan->launches++;
     for (int level = 0; level < 7; level++) {
       HitQueue qin = q[level & 1], qout = q[(level + 1) & 1];

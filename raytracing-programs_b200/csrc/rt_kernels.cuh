@@ -116,10 +116,15 @@ RT_DEV void finish_hit(const DevScene &sc, v3 o, v3 d, float t, int idx, v3 &P, 
 // ---------------------------------------------------------------------------------
 // k_primary: one thread per pixel of the tile (grid-stride).
 // ---------------------------------------------------------------------------------
-#define RT_PRIM_PX 4   // pixels (= primary rays) per thread: one sphere load feeds four reject tests
+template <bool ANY>
+RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_sph, float &best_t, int &best_idx,
+                      unsigned &n_cand, unsigned &n_tests);
+#define RT_PRIM_PX_BRUTE 4   // pixels (= primary rays) per thread: one sphere load feeds four reject tests
+template <bool ACCEL>
 __global__ void __launch_bounds__(256)
 k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict__ c0,
           HitQueue q, int nr_max, unsigned long long *__restrict__ counters) {
+  constexpr int RT_PRIM_PX = ACCEL ? 1 : RT_PRIM_PX_BRUTE;   // the hierarchy walk gains nothing from sharing sphere loads
   const float pw = __fdiv_rn(sc.cam_w, (float)tg.width);    // C/raycast.c:110
   const float ph = __fdiv_rn(sc.cam_h, (float)tg.height);   // C/raycast.c:109
   const double half_w = __ddiv_rn((double)sc.cam_w, 2.0), half_h = __ddiv_rn((double)sc.cam_h, 2.0);
@@ -149,38 +154,49 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
       }
     }
     const int n_live = __popc(live);
-    // spheres: the origin is exactly (0,0,0), so tmp' = -centre and the filter constant k
-    // are per-sphere constants prepared on the host (sph_prim).
-    for (int s = 0; s < sc.n_spheres; s += 2) {
-      const float4 h0 = sc.sph_prim[s], h1 = sc.sph_prim[s + 1];
-      float m0 = -1.0f, m1 = -1.0f;
-      #pragma unroll
+    if constexpr (ACCEL) {
+      // spheres through the bounding-sphere hierarchy (same literal test for whatever it lets through)
+      #pragma unroll 1
       for (int k = 0; k < RT_PRIM_PX; k++) {
-        const float e0 = __fmaf_rn(d[k].z, h0.z, __fmaf_rn(d[k].y, h0.y, d[k].x * h0.x));
-        const float e1 = __fmaf_rn(d[k].z, h1.z, __fmaf_rn(d[k].y, h1.y, d[k].x * h1.x));
-        m0 = fmaxf(m0, __fmaf_rn(e0, e0, h0.w));
-        m1 = fmaxf(m1, __fmaf_rn(e1, e1, h1.w));
+        if (!((live >> k) & 1u)) continue;
+        unsigned nt = 0, nc = 0;
+        bvh_trace<false>(sc, o, d[k], -1, best_t[k], best_idx[k], nc, nt);
+        n_cand += nc; n_sph += nt;
       }
-      if (fmaxf(m0, m1) >= 0.0f) {
-        #pragma unroll 1
-        for (int u = 0; u < 2; u++) {
-          if ((u ? m1 : m0) < 0.0f) continue;
-          const float4 hs = u ? h1 : h0;
-          const float4 sp = sc.sph[s + u];
-          const int idx = sc.sph_idx[s + u];
-          #pragma unroll
-          for (int k = 0; k < RT_PRIM_PX; k++) {
-            const float e = __fmaf_rn(d[k].z, hs.z, __fmaf_rn(d[k].y, hs.y, d[k].x * hs.x));
-            if (__fmaf_rn(e, e, hs.w) >= 0.0f && ((live >> k) & 1u)) {
-              n_cand++;
-              float t;
-              if (sphere_t_literal(o, d[k], sp, t) && better_hit(t, idx, best_t[k], best_idx[k])) { best_t[k] = t; best_idx[k] = idx; }
+    } else {
+      // spheres: the origin is exactly (0,0,0), so tmp' = -centre and the filter constant k
+      // are per-sphere constants prepared on the host (sph_prim).
+      for (int s = 0; s < sc.n_spheres; s += 2) {
+        const float4 h0 = sc.sph_prim[s], h1 = sc.sph_prim[s + 1];
+        float m0 = -1.0f, m1 = -1.0f;
+        #pragma unroll
+        for (int k = 0; k < RT_PRIM_PX; k++) {
+          const float e0 = __fmaf_rn(d[k].z, h0.z, __fmaf_rn(d[k].y, h0.y, d[k].x * h0.x));
+          const float e1 = __fmaf_rn(d[k].z, h1.z, __fmaf_rn(d[k].y, h1.y, d[k].x * h1.x));
+          m0 = fmaxf(m0, __fmaf_rn(e0, e0, h0.w));
+          m1 = fmaxf(m1, __fmaf_rn(e1, e1, h1.w));
+        }
+        if (fmaxf(m0, m1) >= 0.0f) {
+          #pragma unroll 1
+          for (int u = 0; u < 2; u++) {
+            if ((u ? m1 : m0) < 0.0f) continue;
+            const float4 hs = u ? h1 : h0;
+            const float4 sp = sc.sph[s + u];
+            const int idx = sc.sph_idx[s + u];
+            #pragma unroll
+            for (int k = 0; k < RT_PRIM_PX; k++) {
+              const float e = __fmaf_rn(d[k].z, hs.z, __fmaf_rn(d[k].y, hs.y, d[k].x * hs.x));
+              if (__fmaf_rn(e, e, hs.w) >= 0.0f && ((live >> k) & 1u)) {
+                n_cand++;
+                float t;
+                if (sphere_t_literal(o, d[k], sp, t) && better_hit(t, idx, best_t[k], best_idx[k])) { best_t[k] = t; best_idx[k] = idx; }
+              }
             }
           }
         }
       }
+      n_sph += (unsigned long long)sc.n_spheres * n_live;
     }
-    n_sph += (unsigned long long)sc.n_spheres * n_live;
     for (int p = 0; p < sc.n_planes; p++) {
       float4 pp = sc.pln[2 * p], pn = sc.pln[2 * p + 1];
       v3 n = mk3(pn.x, pn.y, pn.z);
@@ -455,9 +471,10 @@ RT_DEV void refl_test_sphere(const DevScene &sc, const v3 P, const v3 dj, const 
 // (|P - Cn| + Rn)^2 for a member of node (Cn, Rn)), so the node sphere is inflated by that much plus the
 // float slack of this test itself; nodes wholly behind the origin (with the larger 2^-6 margin the
 // "both roots negative" argument needs) and, for nearest hit, wholly beyond the best t so far are skipped.
+// obj_sph: sphere slot of the object the ray leaves (-1: none / not a sphere), skipped like C/raycast.c:450.
 // ANY = true: shadow query, returns at the first hit.  Returns whether anything was hit (ANY) / unused.
 template <bool ANY>
-RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj, float &best_t, int &best_idx,
+RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_sph, float &best_t, int &best_idx,
                       unsigned &n_cand, unsigned &n_tests) {
   int stack[32];
   int sp = 0;
@@ -477,13 +494,19 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj,
     if (!ANY && (-en - rinf) > __fmaf_rn(best_t, 1.001f, 4e-3f * reach)) continue;   // whole node beyond the best hit
     const int2 kid = sc.bvh_kids[k];
     if (kid.x >= 0) {
-      stack[sp++] = kid.y; stack[sp++] = kid.x;                // depth <= 28 (host), one net entry per level
+      // children were split along axis (kid.y >> 28), left = lower coordinates: enter the nearer one first
+      // (pushed last), so a nearest-hit search finds a small best_t early and prunes the rest
+      const int axis = kid.y >> 28, right = kid.y & 0x0fffffff;
+      const float da = axis == 0 ? d.x : axis == 1 ? d.y : d.z;
+      const bool left_first = da >= 0.0f;
+      stack[sp++] = left_first ? right : kid.x;                // depth <= 28 (host), one net entry per level
+      stack[sp++] = left_first ? kid.x : right;
     } else {
       const int first = -kid.x - 1;
       for (int i = 0; i < kid.y; i++) {
-        const int ss = sc.bvh_items[first + i];
+        const int ss = first + i;                              // leaves are runs of consecutive sphere slots
         n_tests++;
-        if (sc.sph_idx[ss] == obj) continue;                   // C/raycast.c:450
+        if (ss == obj_sph) continue;                           // C/raycast.c:450
         if (ANY) { if (shadow_hits_sphere(sc, P, d, ss, n_cand)) return true; }
         else refl_test_sphere(sc, P, d, ss, best_t, best_idx, n_cand);
       }
@@ -518,13 +541,13 @@ RT_DEV void scan_quadrics_v(const int nrv, const float (*dsm)[128], unsigned cha
 // ACCEL = true: the sphere part of every shadow query goes through the light buffer (rt_scene.cuh)
 // instead of the bundle scan; the reflection ray still scans every sphere.
 template <int LB, bool QUADS, bool ACCEL>
-__global__ void __launch_bounds__(128, RT_SHADE_MINB)
+__global__ void __launch_bounds__(128, (ACCEL && !QUADS) ? 2 * RT_SHADE_MINB : RT_SHADE_MINB)   // no bundle scan: half the registers, twice the warps
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
         float4 *__restrict__ c0, unsigned long long *__restrict__ counters) {
   constexpr int NR = LB + 1;
   constexpr int VMIN = NR >= 3 ? NR - RT_VSTEP * ((NR - 3) / RT_VSTEP) : NR;   // smallest compiled variant
   auto pick_variant = [](int live) { const int v = NR - RT_VSTEP * ((NR - live) / RT_VSTEP); return v < VMIN ? VMIN : v; };
-  __shared__ unsigned char cand[RT_CHUNK + 1][128];   // +1: the branch-free push stores before it knows
+  __shared__ unsigned char cand[(ACCEL && !QUADS) ? 1 : RT_CHUNK + 1][128];   // +1: the branch-free push stores before it knows
   __shared__ float dsm[3 * NR][128];
   const int tid = threadIdx.x;
   // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
@@ -558,6 +581,8 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
     const float tr = r2.w;
     const float4 m0 = sc.mat[2 * obj], m1 = sc.mat[2 * obj + 1];
     const float refl = m0.w, opacity = m1.w;
+    int obj_sph = -1;                                          // sphere slot of obj (accel mode skips by slot)
+    if constexpr (ACCEL) { const int2 osl = sc.slot[obj]; obj_sph = osl.x == 0 ? osl.y : -1; }
     const bool need_refl = (refl > 0.0f) && (level < 6);   // C/raycast.c:349,352
     const bool lit = opacity > 0.0f;                         // C/raycast.c:385
     n_hp++;
@@ -693,13 +718,13 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
             for (unsigned k = st[0]; k < k1 && !occl; k++) {
               const int ss = sc.lb_items[k];
               o_sph++; d_sph++;
-              if (sc.sph_idx[ss] != obj) occl = shadow_hits_sphere(sc, P, dj, ss, n_cand);   // C/raycast.c:450
+              if (ss != obj_sph) occl = shadow_hits_sphere(sc, P, dj, ss, n_cand);   // C/raycast.c:450
             }
           } else {
             unsigned nt = 0;
             float bt = RT_INF;
             int bi = -1;
-            occl = bvh_trace<true>(sc, P, dj, obj, bt, bi, n_cand, nt);
+            occl = bvh_trace<true>(sc, P, dj, obj_sph, bt, bi, n_cand, nt);
             o_sph += nt; d_sph += nt;
           }
           if (occl) alive &= ~(1u << j);
@@ -707,7 +732,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
         // reflection ray: nearest hit through the bounding-sphere hierarchy
         if (r_on) {
           unsigned nt = 0;
-          bvh_trace<false>(sc, P, rd, obj, best_t, best_idx, n_cand, nt);
+          bvh_trace<false>(sc, P, rd, obj_sph, best_t, best_idx, n_cand, nt);
           o_sph += nt; d_sph += nt; d_slots += nt;
         }
         repack();

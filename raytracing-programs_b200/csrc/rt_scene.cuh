@@ -31,10 +31,10 @@ struct DevScene {
   const float4 *lb_caps;    // [n_lights] squared |P - L| limit of each level {cap0, cap1, cap2, 0}
   // Bounding-sphere hierarchy over the spheres (same opt-in mode): nearest hit of reflection rays and the
   // fallback of shadow rays.  Node k: bvh_node[k] = {centre, radius of a sphere holding all member spheres},
-  // bvh_kids[k] = {left, right} child nodes, or for a leaf {-(first + 1), count} into bvh_items (sphere slots).
+  // bvh_kids[k] = {left, right} child nodes, or for a leaf {-(first + 1), count}: sphere slots first .. first+count-1
+  // (in this mode the host lays the spheres out in leaf order).
   const float4 *bvh_node;
   const int2 *bvh_kids;
-  const int *bvh_items;
 };
 #define RT_LB_RES 32
 #define RT_LB_LEVELS 3
