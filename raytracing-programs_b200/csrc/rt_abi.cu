@@ -175,16 +175,17 @@ void warm_modules() {
 // on the line through L with direction u = (P - L)/|P - L| (the reference sets no t_max, so the part
 // beyond the light counts too: direction -u).  The reference can report a hit on sphere (C, r) only
 // if its float discriminant is >= 0, which by the reject-filter contract needs the line
-// to pass within r_eff = sqrt(r^2 + 2^-17 (T + r^2)) of C, T = |P - C|^2; for |P - L| <= Dcap,
-// T <= (Dcap + |C - L|)^2.  So per light, per distance level (Dcap = 2, 8, 32 x the light's scene
-// radius) and per cube-map cell the list holds every sphere whose cone of half-angle
+// to pass within r_eff = sqrt(r^2 + 2^-18 (T + r^2)) of C, T = |P - C|^2 (the filter's error budget of
+// 35u (T + r^2) plus the roundings of restating it in exact arithmetic: 59u < 2^-18); for |P - L| <= Dcap,
+// T <= (Dcap + |C - L|)^2.  So per light, per distance level (Dcap = 0.35 .. 32 x the light's scene
+// radius: the nearer the hit point, the less the spheres need inflating) and per cube-map cell the list holds every sphere whose cone of half-angle
 // asin(r_eff / |C - L|) around +-(C - L), widened by the cell's own angular radius and a 3e-4 rad
 // margin (float rounding of the direction and of the cell lookup is ~1e-7), meets the cell.
 // Hit points farther than the last level, and degenerate lights, fall back to testing every sphere.
 struct LightBuffer {
   std::vector<unsigned> start;
   std::vector<int> items;
-  std::vector<float4> caps;
+  std::vector<float> caps;
 };
 
 void lb_dir(int face, double s, double t, double *o) {
@@ -279,7 +280,7 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
         }
         cb[3 * c] = b[0]; cb[3 * c + 1] = b[1]; cb[3 * c + 2] = b[2]; cbeta[c] = beta;
       }
-  lb.caps.assign((size_t)nl + 1, make_float4(-1.f, -1.f, -1.f, 0.f));
+  lb.caps.assign((size_t)nl * RT_LB_LEVELS + 1, -1.f);
   std::vector<std::vector<unsigned>> cnt((size_t)nl * RT_LB_LEVELS);           // per (light, level): CSR counts
   std::vector<std::vector<std::pair<int, int>>> pairs((size_t)nl * RT_LB_LEVELS);   // (cell, sphere)
   auto work = [&](int l) {
@@ -293,7 +294,7 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
       if (std::isfinite(d)) Rl = std::max(Rl, d);
     }
     if (!(Rl > 0) || !(Rl < 1e15)) return;
-    const double mult[RT_LB_LEVELS] = {2.0, 8.0, 32.0};
+    const double mult[RT_LB_LEVELS] = {0.35, 0.7, 1.4, 2.8, 8.0, 32.0};
     float capf[RT_LB_LEVELS];
     for (int lv = 0; lv < RT_LB_LEVELS; lv++) {
       const double Dcap = Rl * mult[lv];
@@ -303,7 +304,7 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
         const double dx = sph[s].x - L[0], dy = sph[s].y - L[1], dz = sph[s].z - L[2], r = fabs((double)sph[s].w);
         const double dist = sqrt(dx * dx + dy * dy + dz * dz);
         const double Tcap = (Dcap + dist) * (Dcap + dist);
-        const double reff = sqrt(r * r + ldexp(1.0, -17) * (Tcap + r * r)) + ldexp(8.0, -24) * sqrt(Tcap);
+        const double reff = sqrt(r * r + ldexp(1.0, -18) * (Tcap + r * r)) + ldexp(8.0, -24) * sqrt(Tcap);
         const bool all = !(dist > reff * (1.0 + 1e-6)) || !std::isfinite(reff);
         double a[3] = {0, 0, 0}, theta = 4.0;
         if (!all) { a[0] = dx / dist; a[1] = dy / dist; a[2] = dz / dist; theta = asin(std::min(1.0, reff / dist)) + 3e-4; }
@@ -325,7 +326,7 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
         }
       }
     }
-    lb.caps[l] = make_float4(capf[0], capf[1], capf[2], 0.f);
+    for (int lv = 0; lv < RT_LB_LEVELS; lv++) lb.caps[(size_t)l * RT_LB_LEVELS + lv] = capf[lv];
   };
   {
     std::vector<std::thread> th;
@@ -563,7 +564,7 @@ int rt_scene_upload(const rt_scene *scene) {
       {sph_hot.data(), sph_hot.size() * 16, 0}, {quad_hot.data(), quad_hot.size() * 16, 0},
       {quad_prim.data(), quad_prim.size() * 16, 0},
       {lb.start.data(), have_lb ? lb.start.size() * 4 : 0, 0}, {lb.items.data(), have_lb ? lb.items.size() * 4 : 0, 0},
-      {lb.caps.data(), have_lb ? lb.caps.size() * 16 : 0, 0},
+      {lb.caps.data(), have_lb ? lb.caps.size() * 4 : 0, 0},
       {bvh.node.data(), have_lb ? bvh.node.size() * 16 : 0, 0}, {bvh.kids.data(), have_lb ? bvh.kids.size() * 8 : 0, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
@@ -593,7 +594,7 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.quad_hot = (const float4 *)(b + secs[11].off); sc.quad_prim = (const float4 *)(b + secs[12].off);
     sc.lb_start = have_lb ? (const unsigned *)(b + secs[13].off) : nullptr;
     sc.lb_items = have_lb ? (const int *)(b + secs[14].off) : nullptr;
-    sc.lb_caps = have_lb ? (const float4 *)(b + secs[15].off) : nullptr;
+    sc.lb_caps = have_lb ? (const float *)(b + secs[15].off) : nullptr;
     sc.bvh_node = have_lb ? (const float4 *)(b + secs[16].off) : nullptr;
     sc.bvh_kids = have_lb ? (const int2 *)(b + secs[17].off) : nullptr;
   }

@@ -467,7 +467,8 @@ RT_DEV void refl_test_sphere(const DevScene &sc, const v3 P, const v3 dj, const 
 
 // Traversal of the bounding-sphere hierarchy for one ray.  A node is entered unless the ray certainly
 // misses every member in the REFERENCE's arithmetic: the reference can accept sphere (C, r) only if the
-// line passes within r (1 + 2^-17) + 2^-8 sqrt(T) of C (reject-filter contract, T = |P - C|^2 <=
+// line passes within sqrt(r^2 + 2^-18 (T + r^2)) <= r (1 + 2^-19) + 2^-9 sqrt(T) of C (reject-filter contract:
+// its error budget, 35u (T + r^2), plus the roundings of this restatement, 59u in all; T = |P - C|^2 <=
 // (|P - Cn| + Rn)^2 for a member of node (Cn, Rn)), so the node sphere is inflated by that much plus the
 // float slack of this test itself; nodes wholly behind the origin (with the larger 2^-6 margin the
 // "both roots negative" argument needs) and, for nearest hit, wholly beyond the best t so far are skipped.
@@ -486,7 +487,7 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_
     const float Tn = __fmaf_rn(wz, wz, __fmaf_rn(wy, wy, wx * wx));
     const float en = __fmaf_rn(d.z, wz, __fmaf_rn(d.y, wy, d.x * wx));
     const float reach = sqrtf(Tn) + nd.w;                      // >= sqrt(T) of every member
-    const float rinf = __fmaf_rn(nd.w, 1.0001f, 0.005859375f * reach);   // Rn (1 + 1e-4) + (2^-8 + 2^-9) reach
+    const float rinf = __fmaf_rn(nd.w, 1.0001f, 0.0029296875f * reach);  // Rn (1 + 1e-4) + (2^-9 + 2^-10) reach
     // line misses the inflated node?  (Tn - en^2 is the squared distance, float slack 1e-5 Tn)
     if (!(Tn - en * en <= __fmaf_rn(rinf, rinf, 1e-5f * Tn))) continue;
     const float rbehind = __fmaf_rn(nd.w, 1.001f, 0.015625f * reach);     // Rn (1 + 1e-3) + 2^-6 reach
@@ -708,8 +709,9 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
           const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
           const float wx = lp.x - P.x, wy = lp.y - P.y, wz = lp.z - P.z;
           const float q = __fmaf_rn(wz, wz, __fmaf_rn(wy, wy, wx * wx));
-          const float4 caps = sc.lb_caps[l];
-          const int lv = q <= caps.x ? 0 : q <= caps.y ? 1 : q <= caps.z ? 2 : -1;
+          int lv = -1;
+          #pragma unroll
+          for (int v = RT_LB_LEVELS - 1; v >= 0; v--) lv = q <= sc.lb_caps[l * RT_LB_LEVELS + v] ? v : lv;
           const int cell = lb_cell(-dj.x, -dj.y, -dj.z);
           bool occl = false;
           if (lv >= 0 && cell >= 0) {

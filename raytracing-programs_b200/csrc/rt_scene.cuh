@@ -28,7 +28,7 @@ struct DevScene {
   // reference could report as hit by a shadow ray whose direction seen from the light falls in the cell.
   const unsigned *lb_start; // [n_lights * RT_LB_LEVELS * 6 * RT_LB_RES^2 + 1] CSR starts; NULL = no light buffer
   const int *lb_items;      // sphere slots
-  const float4 *lb_caps;    // [n_lights] squared |P - L| limit of each level {cap0, cap1, cap2, 0}
+  const float *lb_caps;     // [n_lights * RT_LB_LEVELS] squared |P - L| limit of each level, ascending (-1: unusable)
   // Bounding-sphere hierarchy over the spheres (same opt-in mode): nearest hit of reflection rays and the
   // fallback of shadow rays.  Node k: bvh_node[k] = {centre, radius of a sphere holding all member spheres},
   // bvh_kids[k] = {left, right} child nodes, or for a leaf {-(first + 1), count}: sphere slots first .. first+count-1
@@ -37,7 +37,7 @@ struct DevScene {
   const int2 *bvh_kids;
 };
 #define RT_LB_RES 32
-#define RT_LB_LEVELS 3
+#define RT_LB_LEVELS 6
 
 // Cube-map cell of direction u (any length): face = 2 * major axis + (negative ? 1 : 0), the other two
 // components divided by |major| map [-1, 1] onto RT_LB_RES cells.  Returns -1 for a zero or NaN vector.
