@@ -10,3 +10,4 @@ run 8 c4 3 3 scale_c4_n8
 run 8 c5 2 1 scale_c5_n8
 run 4 c4 3 3 scale_c4_n4
 run 2 c4 3 3 scale_c4_n2
+RT_ACCEL=1 run 8 c4 3 3 scale_c4_n8_accel
