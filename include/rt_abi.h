@@ -115,6 +115,12 @@ void rt_shutdown(void);
 const char *rt_last_error(void);
 int rt_abi_version(void);
 
+/* Bound of the reflection loop: MAX_RECURSION of C/raycast.c:14,349 (default 7 = the C program: a pixel sees at
+ * most 6 bounces).  The reference's CUDA and OptiX variants run the same loop with MAX_ITER 50
+ * (CUDA/raycast.cu:13,216); rt_set_max_depth(50) is that mode.  1..64, takes effect at
+ * the next render.  Env RT_MAX_DEPTH in the CLI. */
+int rt_set_max_depth(int depth);
+
 /* Acceleration of the nearest-hit search, read by the next rt_scene_upload.
  * 0 (default): every ray tests every shape, as C/raycast.c:449 does.  1: the sphere part of shadow
  * queries goes through a per-light cube-map "light buffer" built at upload time; the lists are

@@ -31,6 +31,12 @@ gcc $CFLAGS "$TMP/raycast_patched.c" $SUPPORT -o "$OUT/raytrace_ref" -lm
 gcc $CFLAGS "$TMP/raycast_p1.c" $SUPPORT -o "$OUT/raytrace_asis" -lm
 gcc $CFLAGS -fPIC -shared -DREF_RAYCAST_C="\"$TMP/raycast_patched.c\"" \
     "$HERE/ref_harness.c" $SUPPORT -o "$OUT/libref.so" -lm -lpthread
+# Deep-bounce variant of the same harness: MAX_RECURSION 7 -> 50, the bound the reference's own CUDA and OptiX
+# variants use (CUDA/raycast.cu:13 MAX_ITER, Optix/src/deviceCode.cu:5); pins rt_set_max_depth(50).
+sed -e 's|^const int MAX_RECURSION = 7;$|const int MAX_RECURSION = 50;|' "$TMP/raycast_patched.c" > "$TMP/raycast_d50.c"
+grep -q 'MAX_RECURSION = 50;' "$TMP/raycast_d50.c" || { echo "depth patch did not apply" >&2; exit 1; }
+gcc $CFLAGS -fPIC -shared -DREF_RAYCAST_C="\"$TMP/raycast_d50.c\"" \
+    "$HERE/ref_harness.c" $SUPPORT -o "$OUT/libref_d50.so" -lm -lpthread
 echo "built: $(ls "$OUT")"
 # Context comparator: the reference's own CUDA variant, unmodified, rebuilt for
 # sm_100a (its Makefile targets sm_75).  Timed by tools/gpu_refcuda.sh on C1-C3 only: its shared-memory

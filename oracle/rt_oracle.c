@@ -24,7 +24,10 @@
 #include <pthread.h>
 #include "rt_abi.h"
 
-#define MAX_LEVEL 7 /* MAX_RECURSION, C/raycast.c:14 */
+static int g_max_level = 7; /* MAX_RECURSION, C/raycast.c:14; the reference's CUDA/OptiX variants run the same loop
+                               with MAX_ITER 50 (CUDA/raycast.cu:13): orc_set_max_level(50) restates that dormant mode */
+#define MAX_LEVEL g_max_level
+void orc_set_max_level(int n) { g_max_level = n < 1 ? 1 : n; }
 
 typedef struct orc_counters {
   uint64_t rays_primary, rays_reflection, rays_shadow, hit_points;

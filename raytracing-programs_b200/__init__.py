@@ -62,7 +62,7 @@ P3_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p)
 ABI_SYMBOLS = ("rt_init", "rt_init_device", "rt_device_count", "rt_shutdown", "rt_last_error",
                "rt_abi_version", "rt_scene_upload", "rt_render", "rt_render_device", "rt_render_rank",
                "rt_assemble_device", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows",
-               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel")
+               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel", "rt_set_max_depth")
 
 _lib = None
 _host = None
@@ -139,6 +139,10 @@ class Renderer:
         else:
             _check(self.lib, self.lib.rt_init(int(n_gpus)), "rt_init")
         self.scene = None
+
+    def set_max_depth(self, depth):
+        """MAX_RECURSION of C/raycast.c:14 (default 7); 50 = the bound of the reference's CUDA/OptiX variants."""
+        _check(self.lib, self.lib.rt_set_max_depth(int(depth)), "rt_set_max_depth")
 
     def set_accel(self, mode):
         """0: every ray tests every shape (default). 1: light buffer for the sphere part of shadow queries

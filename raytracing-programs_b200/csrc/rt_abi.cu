@@ -82,6 +82,7 @@ DeviceCtx g_dev[RT_MAX_GPUS];
 int g_ndev = 0;
 bool g_have_scene = false;
 int g_n_lights = 0, g_n_shapes = 0;
+int g_max_depth = 7;   // MAX_RECURSION, C/raycast.c:14; rt_set_max_depth
 int g_accel = 0;   // rt_set_accel / RT_ACCEL: light buffer for the sphere part of shadow queries
 
 // ---- NCCL through dlopen ---------------------------------------------------------
@@ -358,6 +359,11 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
 extern "C" {
 
 int rt_abi_version(void) { return RT_ABI_VERSION; }
+int rt_set_max_depth(int depth) {
+  if (depth < 1 || depth > RT_MAX_DEPTH_CAP) return set_err(RT_ERR_ARG, "rt_set_max_depth: depth must be in 1..%d", RT_MAX_DEPTH_CAP);
+  g_max_depth = depth;
+  return RT_OK;
+}
 int rt_set_accel(int mode) {
   if (mode != 0 && mode != 1) return set_err(RT_ERR_ARG, "rt_set_accel: mode must be 0 or 1");
   g_accel = mode;
@@ -416,7 +422,7 @@ int rt_init(int n_gpus) {
     d.sm_count = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
-    CK(cudaMalloc((void **)&d.qcount, 8 * RT_CTL_STRIDE * sizeof(int)));
+    CK(cudaMalloc((void **)&d.qcount, (RT_MAX_DEPTH_CAP + 1) * RT_CTL_STRIDE * sizeof(int)));
     CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
     warm_modules();
   }
@@ -700,7 +706,7 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     tg.width = W; tg.height = H; tg.rank = rank; tg.nranks = nranks; tg.band_h = bh;
     tg.first_px = first;
     tg.n_px = (int)((px_total - first) < (long long)tile ? (px_total - first) : (long long)tile);
-    CK(cudaMemsetAsync(d.qcount, 0, 8 * RT_CTL_STRIDE * sizeof(int), d.stream));
+    CK(cudaMemsetAsync(d.qcount, 0, (RT_MAX_DEPTH_CAP + 1) * RT_CTL_STRIDE * sizeof(int), d.stream));
     HitQueue q0 = q[0]; q0.ctl = d.qcount;
     const int ppx = d.sc.bvh_node ? 1 : RT_PRIM_PX_BRUTE;
     int gp = (tg.n_px + 256 * ppx - 1) / (256 * ppx); if (gp > d.grid_primary) gp = d.grid_primary;
@@ -708,7 +714,8 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     if (d.sc.bvh_node) k_primary<true><<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, lb + 1, d.counters);
     else k_primary<false><<<gp, 256, 0, d.stream>>>(d.sc, tg, d.acc, d.c0, q0, lb + 1, d.counters);
     plan->launches++;
-    for (int level = 0; level < 7; level++) {
+    d.sc.max_depth = g_max_depth;
+    for (int level = 0; level < g_max_depth; level++) {
       HitQueue qin = q[level & 1], qout = q[(level + 1) & 1];
       qin.ctl = d.qcount + level * RT_CTL_STRIDE; qout.ctl = d.qcount + (level + 1) * RT_CTL_STRIDE;
       if ((mr = mark(d, 's')) != RT_OK) return mr;
@@ -930,7 +937,7 @@ int rt_init_device(int ordinal) {
   d.sm_count = prop.multiProcessorCount;
   CK(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&d.ev0)); CK(cudaEventCreate(&d.ev1)); CK(cudaEventCreate(&d.ev2));
-  CK(cudaMalloc((void **)&d.qcount, 8 * RT_CTL_STRIDE * sizeof(int)));
+  CK(cudaMalloc((void **)&d.qcount, (RT_MAX_DEPTH_CAP + 1) * RT_CTL_STRIDE * sizeof(int)));
   CK(cudaMalloc((void **)&d.counters, CT_COUNT * sizeof(unsigned long long)));
   warm_modules();
   g_ndev = 1;

@@ -247,7 +247,7 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
         v3 P, N;
         finish_hit(sc, o, d[k], best_t[k], best_idx[k], P, N);
         queue_push(q, make_float4(P.x, P.y, P.z, __int_as_float(i)), make_float4(N.x, N.y, N.z, __int_as_float(best_idx[k])),
-                   make_float4(d[k].x, d[k].y, d[k].z, 1.0f), hit_class(sc, P, N, best_idx[k], true, nr_max));
+                   make_float4(d[k].x, d[k].y, d[k].z, 1.0f), hit_class(sc, P, N, best_idx[k], sc.max_depth > 1, nr_max));
       }
     }
   }
@@ -584,7 +584,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
     const float refl = m0.w, opacity = m1.w;
     int obj_sph = -1;                                          // sphere slot of obj (accel mode skips by slot)
     if constexpr (ACCEL) { const int2 osl = sc.slot[obj]; obj_sph = osl.x == 0 ? osl.y : -1; }
-    const bool need_refl = (refl > 0.0f) && (level < 6);   // C/raycast.c:349,352
+    const bool need_refl = (refl > 0.0f) && (level < sc.max_depth - 1);   // C/raycast.c:349,352
     const bool lit = opacity > 0.0f;                         // C/raycast.c:385
     n_hp++;
     if (need_refl) n_refl++;
@@ -800,7 +800,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
       finish_hit(sc, P, rd, best_t, best_idx, P2, N2);
       queue_push(qout, make_float4(P2.x, P2.y, P2.z, __int_as_float(pix)), make_float4(N2.x, N2.y, N2.z, __int_as_float(best_idx)),
                  make_float4(rd.x, rd.y, rd.z, mul32(tr, refl)),                  // total_refl, :345,362
-                 hit_class(sc, P2, N2, best_idx, level + 1 < 6, NR));
+                 hit_class(sc, P2, N2, best_idx, level + 1 < sc.max_depth - 1, NR));
     }
   }
   unsigned v[11] = {n_refl, n_lit, n_hp, n_pass_sum, d_sph, n_ls, n_cand, d_pln, d_quad, d_slots, o_sph};

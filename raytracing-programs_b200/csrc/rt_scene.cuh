@@ -7,8 +7,10 @@
 #pragma once
 #include "rt_math.cuh"
 
+#define RT_MAX_DEPTH_CAP 64
 struct DevScene {
   int n_shapes, n_spheres, n_planes, n_quadrics, n_lights;
+  int max_depth;            // MAX_RECURSION of C/raycast.c:14 (7); rt_set_max_depth changes it (dormant deep-bounce mode)
   float cam_w, cam_h;
   const float4 *sph;        // [n_spheres] {cx, cy, cz, r}
   const float4 *sph_hot;    // [n_spheres padded to 4] reject-filter operands {cx, cy, cz, fl(r*r)}; pads never pass

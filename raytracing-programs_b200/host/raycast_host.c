@@ -85,6 +85,8 @@ void raycast(json_data_t *json_struct, PPMFormat photo_data) {
     const char *g = getenv("RT_GPUS");
     if (rt_init(g ? atoi(g) : 1) != RT_OK) fail("cannot initialise the B200 render library");
   }
+  const char *md = getenv("RT_MAX_DEPTH");
+  if (md && rt_set_max_depth(atoi(md)) != RT_OK) fail("bad RT_MAX_DEPTH");
   if (rt_scene_upload(&scene) != RT_OK) fail("scene upload failed");
   if (rt_render(photo_data.width, photo_data.height, photo_data.pixmap, &g_last_stats) != RT_OK)
     fail("render failed");

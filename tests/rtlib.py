@@ -52,8 +52,22 @@ def ref_available():
     return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libref.so"))
 
 
-def ref():
-    global _ref
+_ref_d50 = None
+
+
+def ref(depth=7):
+    """The patched reference harness; depth=50: the same sources with MAX_RECURSION 50 (oracle/build_ref.sh)."""
+    global _ref, _ref_d50
+    if depth == 50:
+        if _ref_d50 is None:
+            r = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libref_d50.so"))
+            r.ref_scene_load.restype = C.c_void_p
+            r.ref_scene_load.argtypes = [C.c_char_p]
+            r.ref_scene_free.argtypes = [C.c_void_p]
+            r.ref_render_row_list.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_int]
+            _ref_d50 = r
+        return _ref_d50
+    assert depth == 7
     if _ref is None:
         r = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libref.so"))
         r.ref_scene_load.restype = C.c_void_p
@@ -83,8 +97,9 @@ def ncores():
         return os.cpu_count() or 1
 
 
-def oracle_render(scene, W, H, rows=None, threads=None, counters=False):
+def oracle_render(scene, W, H, rows=None, threads=None, counters=False, depth=7):
     """Oracle image (all rows, or the given list of rows) as uint8 [n, W, 3]."""
+    oracle().orc_set_max_level(int(depth))
     if isinstance(scene, (str, os.PathLike)):
         scene = pkg.load_scene(scene)
     rows = list(range(H)) if rows is None else list(rows)
@@ -93,11 +108,12 @@ def oracle_render(scene, W, H, rows=None, threads=None, counters=False):
     ct = OrcCounters()
     oracle().orc_render_row_list(C.byref(scene), W, H, arr, len(rows), out.ctypes.data_as(C.c_void_p),
                                  threads or ncores(), C.byref(ct))
+    oracle().orc_set_max_level(7)
     return (out, ct) if counters else out
 
 
-def ref_render(scene_path, W, H, rows=None, threads=None):
-    r = ref()
+def ref_render(scene_path, W, H, rows=None, threads=None, depth=7):
+    r = ref(depth)
     h = r.ref_scene_load(os.fsencode(scene_path))
     if not h:
         raise RuntimeError(f"reference cannot open {scene_path}")
