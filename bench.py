@@ -397,10 +397,12 @@ def main():
     # ---- roofline of the dominant kernel (k_shade) on rank 0 -----------------------------
     shade_ms = agg.ms_shade / max(agg.launches_shade, 1)
     ach = agg.flops_shade / max(agg.ms_shade, 1e-9) / 1e9            # TFLOP/s
-    traffic = None
+    traffic = ncu_ref = None
     try:
         with open(os.path.join(ROOT, "profiles", "k_shade_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
+            tj = json.load(f)
+        traffic = tj.get("dram_bytes_per_launch")
+        ncu_ref = dict(tj.get("ncu") or {}, capture=tj.get("kernel"), file=tj.get("source"))
     except Exception:
         pass
     roof = {"bound": "fp32", "kernel": "k_shade", "achieved": ach, "peak": pk["fp32_tflops"], "unit": "TFLOP/s",
@@ -408,6 +410,8 @@ def main():
             "launches": int(agg.launches_shade), "avg_launch_ms": shade_ms, "kernel_share_of_step": agg.ms_shade / max(agg.ms_kernels, 1e-9),
             "flops_per_launch": agg.flops_shade / max(agg.launches_shade, 1),
             "framebuffer_write_gbs": (W * H * 3 / world) / max(agg.ms_finalize, 1e-9) / 1e6, "hbm_peak_gbs": pk["hbm_gbs"]}
+    if ncu_ref:
+        roof["ncu_capture"] = ncu_ref        # pipe utilisation of the committed ncu capture (not measured in this run)
     if clocks and clocks.get("sm_mhz"):
         roof["frac_at_sampled_clock"] = ach / (FP32_LANES * 2 * clocks["sm_mhz"] * 1e6 / 1e12)
 
