@@ -392,6 +392,39 @@ RT_DEV void scan_chunk(const float (*dsm)[128], unsigned char (*cand)[128], cons
   resolve_spheres(dsm, cand, tid, P, sc, cs, (int)(qp - &cand[0][tid]) >> 7, obj, r_on, alive, best_t, best_idx, n_cand);
 }
 
+// Resolve stage of the quadric scan, shared by all scan variants: filter recheck per ray still alive, then the
+// reference's expression tree (quadric_cq / quadric_t) and the z rule of C/raycast.c:492-494.
+__device__ __noinline__ void resolve_quadrics(const float (*dsm)[128], unsigned char (*cand)[128], const int tid, const v3 P,
+                                              const DevScene &sc, const int cs, const int nc, const int obj, const bool r_on,
+                                              unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
+  for (int i = 0; i < nc; i++) {
+    const int kk = cs + cand[i][tid];
+    const int idx = sc.quad_idx[kk];
+    if (idx == obj) continue;                                  // C/raycast.c:450
+    const QuadFilter f = quad_filter_setup(sc.quad_hot[3 * kk], sc.quad_hot[3 * kk + 1], sc.quad_hot[3 * kk + 2], P.x, P.y, P.z);
+    unsigned pm = 0;
+    for (unsigned m = alive; m; m &= m - 1) {
+      const int j = __ffs(m) - 1;
+      const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+      pm |= (unsigned)(quad_filter_v(f, dj) >= 0.0f) << j;
+    }
+    if (!pm) continue;
+    const quad10 qq = load_quad(sc.quad, kk);
+    const float c_q = (float)quadric_cq(P, qq);
+    for (; pm; pm &= pm - 1) {
+      const int j = __ffs(pm) - 1;
+      const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+      float t;
+      n_cand++;
+      if (quadric_t(P, dj, qq, c_q, t)) {
+        if (add32(P.z, mul32(t, dj.z)) < P.z) continue;       // C/raycast.c:492-494 (skip_index != -1 here)
+        if (r_on && j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
+        else if (t > 0.0f && t < RT_INF) alive &= ~(1u << j);
+      }
+    }
+  }
+}
+
 // Quadric scan of one chunk, same structure as scan_chunk: conservative FP32 reject filter
 // (rt_math.cuh, "quadric filter") for NRV rays in registers, survivors queued per thread and
 // resolved by the reference's expression tree (quadric_cq / quadric_t, mixed float/double)
@@ -417,31 +450,7 @@ RT_DEV void scan_quadrics(const float (*dsm)[128], unsigned char (*cand)[128], c
     *qp = (unsigned char)k;
     qp += (vmax >= 0.0f) ? 128 : 0;
   }
-  const int nc = (int)(qp - &cand[0][tid]) >> 7;
-  for (int i = 0; i < nc; i++) {
-    const int kk = cs + cand[i][tid];
-    const int idx = sc.quad_idx[kk];
-    if (idx == obj) continue;                                  // C/raycast.c:450
-    const QuadFilter f = quad_filter_setup(sc.quad_hot[3 * kk], sc.quad_hot[3 * kk + 1], sc.quad_hot[3 * kk + 2], P.x, P.y, P.z);
-    unsigned pm = 0;
-    #pragma unroll
-    for (int j = 0; j < NRV; j++) pm |= (unsigned)(quad_filter_v(f, d[j]) >= 0.0f) << j;
-    pm &= alive;
-    if (!pm) continue;
-    const quad10 qq = load_quad(sc.quad, kk);
-    const float c_q = (float)quadric_cq(P, qq);
-    for (; pm; pm &= pm - 1) {
-      const int j = __ffs(pm) - 1;
-      const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
-      float t;
-      n_cand++;
-      if (quadric_t(P, dj, qq, c_q, t)) {
-        if (add32(P.z, mul32(t, dj.z)) < P.z) continue;       // C/raycast.c:492-494 (skip_index != -1 here)
-        if (r_on && j == 0) { if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; } }
-        else if (t > 0.0f && t < RT_INF) alive &= ~(1u << j);
-      }
-    }
-  }
+  resolve_quadrics(dsm, cand, tid, P, sc, cs, (int)(qp - &cand[0][tid]) >> 7, obj, r_on, alive, best_t, best_idx, n_cand);
 }
 
 // One shadow ray (origin P, direction dj) against sphere slot ss: does the reference report a hit with
