@@ -264,7 +264,7 @@ bool build_sphere_bvh(const std::vector<float4> &sph, int n_sph, SphereBvh &out)
 
 bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, int n_sph, LightBuffer &lb) {
   const int R = RT_LB_RES, CELLS = 6 * R * R, nl = scene->num_lights;
-  std::vector<double> cb(3 * (size_t)CELLS), cbeta(CELLS);
+  std::vector<double> cb(3 * (size_t)CELLS), cbeta(CELLS), ccos(CELLS), csin(CELLS);
   for (int face = 0; face < 6; face++)
     for (int j = 0; j < R; j++)
       for (int i = 0; i < R; i++) {
@@ -280,6 +280,26 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
           beta = std::max(beta, acos(d));
         }
         cb[3 * c] = b[0]; cb[3 * c + 1] = b[1]; cb[3 * c + 2] = b[2]; cbeta[c] = beta;
+        ccos[c] = cos(beta); csin[c] = sin(beta);
+      }
+  // 4 x 4 blocks of cells: centre direction and angular radius, to skip 16 cells with one test
+  const int RB = R / 4;
+  std::vector<double> bb(3 * (size_t)6 * RB * RB), bbeta((size_t)6 * RB * RB);
+  for (int face = 0; face < 6; face++)
+    for (int j = 0; j < RB; j++)
+      for (int i = 0; i < RB; i++) {
+        const double s0 = -1.0 + 8.0 * i / R, s1 = -1.0 + 8.0 * (i + 1) / R, t0 = -1.0 + 8.0 * j / R, t1 = -1.0 + 8.0 * (j + 1) / R;
+        double b[3], q[3], beta = 0;
+        lb_dir(face, 0.5 * (s0 + s1), 0.5 * (t0 + t1), b);
+        const double cs[4][2] = {{s0, t0}, {s1, t0}, {s0, t1}, {s1, t1}};
+        for (auto &k : cs) {
+          lb_dir(face, k[0], k[1], q);
+          double d = b[0] * q[0] + b[1] * q[1] + b[2] * q[2];
+          d = d > 1 ? 1 : d < -1 ? -1 : d;
+          beta = std::max(beta, acos(d));
+        }
+        const int blk = (face * RB + j) * RB + i;
+        bb[3 * blk] = b[0]; bb[3 * blk + 1] = b[1]; bb[3 * blk + 2] = b[2]; bbeta[blk] = beta + 1e-9;
       }
   lb.caps.assign((size_t)nl * RT_LB_LEVELS + 1, -1.f);
   std::vector<std::vector<unsigned>> cnt((size_t)nl * RT_LB_LEVELS);           // per (light, level): CSR counts
@@ -314,16 +334,33 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
             const double ax = fabs(a[face >> 1]), reach = theta + 0.9555;
             if (reach < 1.5707 && ax < cos(reach)) continue;
           }
-          for (int k = 0; k < R * R; k++) {
-            const int c = face * R * R + k;
-            bool in = all;
-            if (!in) {
-              const double ang = theta + cbeta[c];
-              if (ang >= 3.14159) in = true;
-              else { const double dd = cb[3 * c] * a[0] + cb[3 * c + 1] * a[1] + cb[3 * c + 2] * a[2]; in = fabs(dd) >= cos(ang) || cos(ang) <= 0; }
+          const double ct = all ? 0 : cos(theta), st = all ? 0 : sin(theta);
+          for (int bj = 0; bj < RB; bj++)
+            for (int bi = 0; bi < RB; bi++) {
+              if (!all) {   // whole block out of reach of both +a and -a?
+                const int blk = (face * RB + bj) * RB + bi;
+                const double ang = theta + bbeta[blk];
+                if (ang < 3.14159) {
+                  const double dd = bb[3 * blk] * a[0] + bb[3 * blk + 1] * a[1] + bb[3 * blk + 2] * a[2];
+                  const double ca = cos(ang);
+                  if (ca > 0 && fabs(dd) < ca) continue;
+                }
+              }
+              for (int cj = 4 * bj; cj < 4 * bj + 4; cj++)
+                for (int ci = 4 * bi; ci < 4 * bi + 4; ci++) {
+                  const int c = (face * R + cj) * R + ci;
+                  bool in = all;
+                  if (!in) {
+                    if (theta + cbeta[c] >= 3.14159) in = true;
+                    else {
+                      const double ca = ct * ccos[c] - st * csin[c];   // cos(theta + beta_c)
+                      const double dd = cb[3 * c] * a[0] + cb[3 * c + 1] * a[1] + cb[3 * c + 2] * a[2];
+                      in = ca <= 0 || fabs(dd) >= ca - 1e-12;
+                    }
+                  }
+                  if (in) pv.push_back(std::make_pair(c, s));
+                }
             }
-            if (in) pv.push_back(std::make_pair(c, s));
-          }
         }
       }
     }
