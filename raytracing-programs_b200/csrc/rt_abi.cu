@@ -598,7 +598,9 @@ int rt_scene_upload(const rt_scene *scene) {
   const bool have_lb = have_bvh && nl > 0 && n_sph_real > 0 && build_light_buffer(scene, sph, n_sph_real, lb);
   // one blob, 256-byte aligned sections
   struct Sec { const void *src; size_t bytes; size_t off; };
-  Sec secs[18] = {
+  std::vector<float4> lb_hot;
+  if (have_lb) { lb_hot.resize(lb.items.size()); for (size_t k = 0; k + 1 < lb.items.size(); k++) lb_hot[k] = sph_hot[lb.items[k]]; }
+  Sec secs[19] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
@@ -608,7 +610,8 @@ int rt_scene_upload(const rt_scene *scene) {
       {quad_prim.data(), quad_prim.size() * 16, 0},
       {lb.start.data(), have_lb ? lb.start.size() * 4 : 0, 0}, {lb.items.data(), have_lb ? lb.items.size() * 4 : 0, 0},
       {lb.caps.data(), have_lb ? lb.caps.size() * 4 : 0, 0},
-      {bvh.node.data(), have_lb ? bvh.node.size() * 16 : 0, 0}, {bvh.kids.data(), have_lb ? bvh.kids.size() * 8 : 0, 0}};
+      {bvh.node.data(), have_lb ? bvh.node.size() * 16 : 0, 0}, {bvh.kids.data(), have_lb ? bvh.kids.size() * 8 : 0, 0},
+      {lb_hot.data(), have_lb ? lb_hot.size() * 16 : 0, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -640,6 +643,7 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.lb_caps = have_lb ? (const float *)(b + secs[15].off) : nullptr;
     sc.bvh_node = have_lb ? (const float4 *)(b + secs[16].off) : nullptr;
     sc.bvh_kids = have_lb ? (const int2 *)(b + secs[17].off) : nullptr;
+    sc.lb_hot = have_lb ? (const float4 *)(b + secs[18].off) : nullptr;
   }
   g_have_scene = true;
   g_n_lights = nl;

@@ -456,8 +456,7 @@ RT_DEV void scan_quadrics(const float (*dsm)[128], unsigned char (*cand)[128], c
 // One shadow ray (origin P, direction dj) against sphere slot ss: does the reference report a hit with
 // 0 < t < inf?  Same decision chain as the resolve stage of scan_chunk: conservative filter, sign
 // analysis where the margins allow it, the reference's literal root otherwise.
-RT_DEV bool shadow_hits_sphere(const DevScene &sc, const v3 P, const v3 dj, const int ss, unsigned &n_cand) {
-  const float4 hh = sc.sph_hot[ss];
+RT_DEV bool shadow_hits_sphere(const DevScene &sc, const v3 P, const v3 dj, const int ss, const float4 hh, unsigned &n_cand) {
   const float xs = P.x - hh.x, ys = P.y - hh.y, zs = P.z - hh.z;
   const float Ts = __fmaf_rn(zs, zs, __fmaf_rn(ys, ys, xs * xs));
   const float cp = Ts - hh.w, marg = RT_FILTER_EPS * (Ts + hh.w);
@@ -537,7 +536,7 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_
         const int ss = first + i;                              // leaves are runs of consecutive sphere slots
         n_tests++;
         if (ss == obj_sph) continue;                           // C/raycast.c:450
-        if (ANY) { if (shadow_hits_sphere(sc, P, d, ss, n_cand)) return true; }
+        if (ANY) { if (shadow_hits_sphere(sc, P, d, ss, sc.sph_hot[ss], n_cand)) return true; }
         else refl_test_sphere(sc, P, d, ss, best_t, best_idx, n_cand);
       }
     }
@@ -748,8 +747,9 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
             const unsigned k1 = st[1];
             for (unsigned k = st[0]; k < k1 && !occl; k++) {
               const int ss = sc.lb_items[k];
+              const float4 hh = sc.lb_hot[k];                   // the sphere's filter operands, stored with the list
               o_sph++; d_sph++;
-              if (ss != obj_sph) occl = shadow_hits_sphere(sc, P, dj, ss, n_cand);   // C/raycast.c:450
+              if (ss != obj_sph) occl = shadow_hits_sphere(sc, P, dj, ss, hh, n_cand);   // C/raycast.c:450
             }
           } else {
             unsigned nt = 0;

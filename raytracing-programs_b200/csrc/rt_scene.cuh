@@ -30,6 +30,7 @@ struct DevScene {
   // reference could report as hit by a shadow ray whose direction seen from the light falls in the cell.
   const unsigned *lb_start; // [n_lights * RT_LB_LEVELS * 6 * RT_LB_RES^2 + 1] CSR starts; NULL = no light buffer
   const int *lb_items;      // sphere slots
+  const float4 *lb_hot;     // sph_hot of each item, so walking a list costs no dependent load
   const float *lb_caps;     // [n_lights * RT_LB_LEVELS] squared |P - L| limit of each level, ascending (-1: unusable)
   // Bounding-sphere hierarchy over the spheres (same opt-in mode): nearest hit of reflection rays and the
   // fallback of shadow rays.  Node k: bvh_node[k] = {centre, radius of a sphere holding all member spheres},
