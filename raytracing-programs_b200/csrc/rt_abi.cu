@@ -59,7 +59,7 @@ struct DeviceCtx {
   size_t tile_cap = 0;
   float4 *acc = nullptr, *c0 = nullptr;
   float4 *qbuf = nullptr;     // 6 * tile_cap float4: two queues x {r0,r1,r2}
-  int *qcount = nullptr;      // [8 levels][RT_CTL_STRIDE] queue control words (HitQueue::ctl)
+  int *qcount = nullptr;      // [RT_MAX_DEPTH_CAP + 1 levels][RT_CTL_STRIDE] queue control words (HitQueue::ctl)
   int *qcls = nullptr;        // 2 queues x RT_NCLS x tile_cap class lists
   unsigned long long *counters = nullptr;
   // output
