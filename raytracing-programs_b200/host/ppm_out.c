@@ -43,9 +43,59 @@ void ppm_WriteOutP3(PPMFormat inData, FILE *outFile) {
   }
 }
 
+/*
+ * The binary writers (C/ppm.c:193-227).  The reference wrote them for an RGBA pixmap (they come
+ * from its PPM converter: P6 drops every fourth byte through ppm_RemoveAlphaChannel, P7 writes
+ * 4 bytes per pixel) and never calls them from the raytracer, whose pixmap is RGB.  Here
+ * inData.depth says which one the caller holds: 4 = RGBA, byte for byte what the reference
+ * emits; anything else = RGB as raycast() leaves it (P6 writes it as is, P7 adds an opaque
+ * alpha = maxColor).  Both end with the reference's trailing newline after the raster.
+ * Not part of the hot path: the frame is already in host memory and this is an fwrite.
+ */
+#define PPM_CHUNK_PIXELS (1u << 18)
+
 void ppm_WriteOutP6(PPMFormat inData, FILE *outFile) {
-  fprintf(outFile, "P6\n%d %d\n%u\n", inData.width, inData.height, inData.maxColor);
-  fwrite(inData.pixmap, 1, (size_t)inData.width * (size_t)inData.height * 3u, outFile);
+  const size_t n = (size_t)inData.width * (size_t)inData.height;
+  fprintf(outFile, "P6\n%d %d\n%d\n", inData.width, inData.height, inData.maxColor);
+  if (inData.depth != 4) {
+    fwrite(inData.pixmap, 1, n * 3u, outFile);
+  } else {
+    uint8_t *buf = (uint8_t *)malloc((size_t)PPM_CHUNK_PIXELS * 3u);
+    if (buf == NULL) { fprintf(stderr, "Error: out of memory in the P6 writer\n"); exit(1); }
+    for (size_t p0 = 0; p0 < n; p0 += PPM_CHUNK_PIXELS) {
+      const size_t m = n - p0 < PPM_CHUNK_PIXELS ? n - p0 : PPM_CHUNK_PIXELS;
+      const uint8_t *src = inData.pixmap + p0 * 4u;
+      for (size_t i = 0; i < m; i++) {
+        buf[3 * i] = src[4 * i]; buf[3 * i + 1] = src[4 * i + 1]; buf[3 * i + 2] = src[4 * i + 2];
+      }
+      fwrite(buf, 1, m * 3u, outFile);
+    }
+    free(buf);
+  }
+  fputc('\n', outFile);
+}
+
+void ppm_WriteOutP7(PPMFormat inData, FILE *outFile) {
+  const size_t n = (size_t)inData.width * (size_t)inData.height;
+  fprintf(outFile, "P7\nWIDTH %d\nHEIGHT %d\nDEPTH %d\nMAXVAL %d\nTUPLTYPE RGB_ALPHA\n",
+          inData.width, inData.height, 4, inData.maxColor);
+  if (inData.depth == 4) {
+    fwrite(inData.pixmap, 1, n * 4u, outFile);
+  } else {
+    uint8_t *buf = (uint8_t *)malloc((size_t)PPM_CHUNK_PIXELS * 4u);
+    if (buf == NULL) { fprintf(stderr, "Error: out of memory in the P7 writer\n"); exit(1); }
+    for (size_t p0 = 0; p0 < n; p0 += PPM_CHUNK_PIXELS) {
+      const size_t m = n - p0 < PPM_CHUNK_PIXELS ? n - p0 : PPM_CHUNK_PIXELS;
+      const uint8_t *src = inData.pixmap + p0 * 3u;
+      for (size_t i = 0; i < m; i++) {
+        buf[4 * i] = src[3 * i]; buf[4 * i + 1] = src[3 * i + 1]; buf[4 * i + 2] = src[3 * i + 2];
+        buf[4 * i + 3] = inData.maxColor;
+      }
+      fwrite(buf, 1, m * 4u, outFile);
+    }
+    free(buf);
+  }
+  fputc('\n', outFile);
 }
 
 float ppm_clamp(float value, float lower_bound, float upper_bound) {

@@ -23,7 +23,9 @@ void ppm_WriteOutP3(PPMFormat inData, FILE *outFile);   /* C/ppm.c:168-184 */
 /* The pixmap passed to the next ppm_WriteOutP3 calls is exactly what raycast() rendered last
  * (untouched since): format the frame still resident on GPU 0 instead of uploading it. */
 void rt_host_p3_resident(int yes);
-void ppm_WriteOutP6(PPMFormat inData, FILE *outFile);   /* C/ppm.c:193-200, raw variant */
+/* Binary writers; inData.depth == 4: RGBA pixmap (the reference's assumption), else RGB. */
+void ppm_WriteOutP6(PPMFormat inData, FILE *outFile);   /* C/ppm.c:193-203 */
+void ppm_WriteOutP7(PPMFormat inData, FILE *outFile);   /* C/ppm.c:212-227 */
 float ppm_clamp(float value, float lower_bound, float upper_bound); /* C/ppm.c:350-359 */
 
 #ifdef __cplusplus

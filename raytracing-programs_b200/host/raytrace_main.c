@@ -80,7 +80,8 @@ int main(int argc, char **argv) {
   raycast(json_struct, photo_data);
   double rendered = now_sec();
   rt_host_p3_resident(1);   /* nothing touched the pixmap since raycast() (as in C/raycast.c:57-59) */
-  if (getenv("RT_PPM_P6")) ppm_WriteOutP6(photo_data, output_image);
+  if (getenv("RT_PPM_P7")) ppm_WriteOutP7(photo_data, output_image);
+  else if (getenv("RT_PPM_P6")) ppm_WriteOutP6(photo_data, output_image);
   else ppm_WriteOutP3(photo_data, output_image);
   fclose(output_image);
   free(photo_data.pixmap);

@@ -1,6 +1,7 @@
 """CPU tests of the host side: parser parity and error paths, the C-ABI
 library's exported symbols, band ownership helpers, loud failure without a GPU."""
 import ctypes as C
+import json
 import os
 import re
 import subprocess
@@ -177,3 +178,64 @@ def test_parser_hardening(tmp_path):
     sc = pkg.load_scene(str(big))
     assert sc.num_shapes == 5000 and sc.shapes[4999].position[0] == float(4999 % 70 - 35)
     assert time.perf_counter() - t0 < 5.0
+
+
+# ------------------------------------------------------- binary writers (C/ppm.c:193-227)
+class _PPM(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("size", C.c_int), ("maxColor", C.c_uint8),
+                ("depth", C.c_uint8), ("tupleType", C.c_char_p), ("pixmap", C.POINTER(C.c_uint8))]
+
+
+def _write_with(lib, fn, W, H, depth, px, path, max_color=255):
+    libc = C.CDLL(None)
+    libc.fopen.restype = C.c_void_p
+    libc.fopen.argtypes = [C.c_char_p, C.c_char_p]
+    libc.fclose.argtypes = [C.c_void_p]
+    f = getattr(lib, fn)
+    f.argtypes = [_PPM, C.c_void_p]
+    f.restype = None
+    fp = libc.fopen(os.fsencode(path), b"wb")
+    f(_PPM(W, H, W * H * 3, max_color, depth, None, px.ctypes.data_as(C.POINTER(C.c_uint8))), fp)
+    libc.fclose(fp)
+    return open(path, "rb").read()
+
+
+BIN_CASES = [(1, 1), (7, 5), (640, 480), (1000, 263)]      # the last one spans several writer chunks
+
+
+def _rgba(W, H, alpha=255):
+    rgb = rtlib.p3_pixmap(W, H, "random").reshape(-1, 3)
+    return np.ascontiguousarray(np.concatenate([rgb, np.full((W * H, 1), alpha, np.uint8)], axis=1)), np.ascontiguousarray(rgb)
+
+
+def test_binary_writers_golden(tmp_path):
+    """ppm_WriteOutP6 / ppm_WriteOutP7 of the host against hashes of the files the reference's own
+    writers produce for the same RGBA pixmaps (tests/golden/make_bin_golden.py), and the RGB entry
+    (depth 3, the raytracer's pixmap) against the same files."""
+    import hashlib
+    h = rtlib.pkg.load_host_library()
+    gold = json.load(open(os.path.join(rtlib.GOLDEN, "bin_hashes.json")))
+    for W, H in BIN_CASES:
+        rgba, rgb = _rgba(W, H)
+        for fn in ("ppm_WriteOutP6", "ppm_WriteOutP7"):
+            a = _write_with(h, fn, W, H, 4, rgba, tmp_path / "a.ppm")
+            b = _write_with(h, fn, W, H, 3, rgb, tmp_path / "b.ppm")
+            g = gold[f"{fn}_{W}x{H}"]
+            assert hashlib.md5(a).hexdigest() == g["md5"] and len(a) == g["bytes"], (fn, W, H)
+            assert a == b, (fn, W, H)
+    # known answer
+    px = np.array([1, 2, 3], np.uint8)
+    assert _write_with(h, "ppm_WriteOutP7", 1, 1, 3, px, tmp_path / "c.ppm", 200) == \
+        b"P7\nWIDTH 1\nHEIGHT 1\nDEPTH 4\nMAXVAL 200\nTUPLTYPE RGB_ALPHA\n\x01\x02\x03\xc8\n"
+    assert _write_with(h, "ppm_WriteOutP6", 1, 1, 3, px, tmp_path / "d.ppm") == b"P6\n1 1\n255\n\x01\x02\x03\n"
+
+
+@pytest.mark.skipif(not rtlib.ref_available(), reason="oracle/_ref not built")
+def test_binary_writers_match_reference(tmp_path):
+    h = rtlib.pkg.load_host_library()
+    r = rtlib.ref()
+    for W, H in BIN_CASES:
+        rgba, _ = _rgba(W, H, alpha=77)
+        for fn in ("ppm_WriteOutP6", "ppm_WriteOutP7"):
+            assert _write_with(h, fn, W, H, 4, rgba, tmp_path / "a.ppm") == \
+                _write_with(r, fn, W, H, 4, rgba, tmp_path / "r.ppm"), (fn, W, H)
