@@ -123,10 +123,35 @@ int rt_set_max_depth(int depth);
 
 /* Acceleration of the nearest-hit search, read by the next rt_scene_upload.
  * 0 (default): every ray tests every shape, as C/raycast.c:449 does.  1: the sphere part of shadow
- * queries goes through a per-light cube-map "light buffer" built at upload time; the lists are
- * conservative with respect to the reference's float arithmetic, so the image is the same, byte
- * for byte.  Env RT_ACCEL=0/1 overrides. */
+ * queries goes through a per-light cube-map "light buffer" built at upload time, every other sphere
+ * search and the searches over the ellipsoids among the quadrics through bounding-sphere hierarchies;
+ * all of it is conservative with respect to the reference's float arithmetic, so the image is the
+ * same, byte for byte.  Env RT_ACCEL=0/1 overrides. */
 int rt_set_accel(int mode);
+
+/* Diagnostics of the quadric index of the accelerated mode (csrc/rt_qindex.cuh); host arithmetic only, no GPU
+ * needed.  tests/test_qindex.py drives them against the oracle's quadric intersector (C/raycast.c:614-656) to
+ * check that the index can only drop quadrics the reference would not report.
+ * rt_dbg_qindex_classify: q10 = a..j of one quadric; returns 1 and fills `out` if the quadric is an ellipsoid
+ * the index can hold, else 0.
+ * rt_dbg_qindex_prune: the traversal's node test for node4 = {centre, radius}, n_rays rays (P3[3n], d3[3n],
+ * best_t[n] when nearest != 0) and consts5 as in rt_qindex_info; codes[n]: 0 enter, 1 line misses, 2 behind
+ * the origin, 3 beyond best_t.  Returns 0. */
+typedef struct rt_qindex_info {
+  double centre[3], K, lmin, lmax;
+  double delta[3];                     /* inflation of the level set for an origin at distance s: d0 + d1 s + d2 s^2 */
+  float ball[4];                       /* bounding sphere {cx, cy, cz, r} the index stores */
+  float consts[5];                     /* miss_rel, behind_rel, behind_abs, t_rel, t_abs */
+} rt_qindex_info;
+int rt_dbg_qindex_classify(const float *q10, rt_qindex_info *out);
+int rt_dbg_qindex_prune(const float *node4, const float *P3, const float *d3, int n_rays, int nearest,
+                        const float *best_t, const float *consts5, int *codes);
+/* Builds the index over n_quadrics quadrics (q10[10 n]) exactly as rt_scene_upload does and walks it on the host
+ * for n_rays rays: visited[r * n_quadrics + k] = 1 if the traversal would test quadric k for ray r (quadrics the
+ * index does not hold are always tested).  nearest != 0: nearest-hit search pruned with the fixed best_t[r].
+ * Returns the number of indexed quadrics, -1 on bad arguments. */
+int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const float *d3, int n_rays, int nearest,
+                        const float *best_t, unsigned char *visited);
 
 /* Flatten to type-sorted SoA (+ original index) and upload to every device in use.
  * Takes the place of the list->VLA copy at C/raycast.c:87-107. The scene is copied;

@@ -323,6 +323,13 @@ int orc_isect_quadric(const float *o, const float *d, const float *q10, float *t
   return isect_quadric(o, d, &s, t);
 }
 
+/* n rays against one quadric (tests/test_qindex.py): hit[r] = the intersector's return value, t[r] its distance */
+void orc_isect_quadric_batch(const float *o3, const float *d3, const float *q10, int n, int *hit, float *t) {
+  rt_shape s; memset(&s, 0, sizeof s); s.type = RT_QUADRIC;
+  for (int k = 0; k < 10; k++) s.params[k] = q10[k];
+  for (int r = 0; r < n; r++) { t[r] = 0.0f; hit[r] = isect_quadric(o3 + 3 * r, d3 + 3 * r, &s, &t[r]); }
+}
+
 /* ---- P3 writer restatement (C/ppm.c:168-184): "P3\n", "%d %d \n%u\n", then per pixel
  * "%d\n%d\n%d\n" of the three channel bytes, rows top to bottom.  Writes into out (capacity
  * cap) and returns the length, or 0 when cap is too small.  size_t indexing (the reference's

@@ -62,7 +62,8 @@ P3_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p)
 ABI_SYMBOLS = ("rt_init", "rt_init_device", "rt_device_count", "rt_shutdown", "rt_last_error",
                "rt_abi_version", "rt_scene_upload", "rt_render", "rt_render_device", "rt_render_rank",
                "rt_assemble_device", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows",
-               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel", "rt_set_max_depth")
+               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel", "rt_set_max_depth",
+               "rt_dbg_qindex_classify", "rt_dbg_qindex_prune", "rt_dbg_qindex_visit")
 
 _lib = None
 _host = None

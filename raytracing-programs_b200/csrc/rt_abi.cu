@@ -262,6 +262,52 @@ bool build_sphere_bvh(const std::vector<float4> &sph, int n_sph, SphereBvh &out)
   return n_sph > 0 && bvh_build_rec(sph, ids, 0, n_sph, 0, out, &root);
 }
 
+// Index over the ellipsoids among a list of quadrics (rt_qindex.cuh).  order: positions of the input list, the
+// n_idx certified ellipsoids first in the leaf order of their bounding-sphere hierarchy, then everything else in
+// input order.  marg: per node {miss_rel, behind_abs, t_rel, t_abs}, the largest margins its members need.
+struct QuadricIndex {
+  std::vector<int> order;
+  int n_idx = 0;
+  SphereBvh bvh;
+  std::vector<float4> marg;
+  float behind_rel = 0.f;
+};
+
+void build_quadric_index(const std::vector<const float *> &params, QuadricIndex &out) {
+  std::vector<int> idxd, rest;
+  std::vector<float4> balls, marg;
+  out = QuadricIndex();
+  for (size_t k = 0; k < params.size(); k++) {
+    QIndexItem it;
+    qindex_classify(params[k], it);
+    // an ellipsoid whose certified bounding sphere is out of proportion gains nothing from the index
+    if (it.ok && it.r_item <= 4.0 * sqrt(it.K / it.lmin)) {
+      idxd.push_back((int)k);
+      balls.push_back(make_float4(it.centre[0], it.centre[1], it.centre[2], it.r_item));
+      marg.push_back(make_float4(it.miss_rel, it.behind_abs, it.t_rel, it.t_abs));
+      out.behind_rel = std::max(out.behind_rel, it.behind_rel);
+    } else rest.push_back((int)k);
+  }
+  if (idxd.size() >= 8 && build_sphere_bvh(balls, (int)balls.size(), out.bvh)) {
+    out.n_idx = (int)idxd.size();
+    for (int k : out.bvh.items) out.order.push_back(idxd[k]);
+    out.order.insert(out.order.end(), rest.begin(), rest.end());
+    // children are created after their parent, so one backward sweep folds the members' margins upwards
+    auto fold = [](float4 x, float4 y) { return make_float4(std::max(x.x, y.x), std::max(x.y, y.y), std::max(x.z, y.z), std::max(x.w, y.w)); };
+    out.marg.assign(out.bvh.node.size(), make_float4(0.f, 0.f, 0.f, 0.f));
+    for (int k = (int)out.bvh.node.size() - 1; k >= 0; k--) {
+      const int2 kid = out.bvh.kids[k];
+      if (kid.x >= 0) out.marg[k] = fold(out.marg[kid.x], out.marg[kid.y & 0x0fffffff]);
+      else for (int i = 0; i < kid.y; i++) out.marg[k] = fold(out.marg[k], marg[out.bvh.items[-kid.x - 1 + i]]);
+    }
+  } else {
+    out.bvh = SphereBvh();
+    out.behind_rel = 0.f;
+    out.order.resize(params.size());
+    for (size_t k = 0; k < params.size(); k++) out.order[k] = (int)k;
+  }
+}
+
 bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, int n_sph, LightBuffer &lb) {
   const int R = RT_LB_RES, CELLS = 6 * R * R, nl = scene->num_lights;
   std::vector<double> cb(3 * (size_t)CELLS), cbeta(CELLS), ccos(CELLS), csin(CELLS);
@@ -401,6 +447,57 @@ int rt_set_max_depth(int depth) {
   g_max_depth = depth;
   return RT_OK;
 }
+int rt_dbg_qindex_classify(const float *q10, rt_qindex_info *out) {
+  if (!q10 || !out) return 0;
+  QIndexItem it;
+  qindex_classify(q10, it);
+  if (!it.ok) return 0;
+  for (int k = 0; k < 3; k++) { out->centre[k] = it.c[k]; out->ball[k] = it.centre[k]; }
+  out->K = it.K; out->lmin = it.lmin; out->lmax = it.lmax;
+  out->delta[0] = it.a0; out->delta[1] = it.a1; out->delta[2] = it.a2;
+  out->ball[3] = it.r_item;
+  out->consts[0] = it.miss_rel; out->consts[1] = it.behind_rel; out->consts[2] = it.behind_abs;
+  out->consts[3] = it.t_rel; out->consts[4] = it.t_abs;
+  return 1;
+}
+
+int rt_dbg_qindex_prune(const float *node4, const float *P3, const float *d3, int n_rays, int nearest, const float *best_t,
+                        const float *consts5, int *codes) {
+  const QIndexConsts k = {consts5[0], consts5[1], consts5[2], consts5[3], consts5[4]};
+  const float4 nd = make_float4(node4[0], node4[1], node4[2], node4[3]);
+  for (int r = 0; r < n_rays; r++)
+    codes[r] = qnode_prune(nd, P3[3 * r], P3[3 * r + 1], P3[3 * r + 2], d3[3 * r], d3[3 * r + 1], d3[3 * r + 2], nearest != 0,
+                           nearest ? best_t[r] : 0.0f, k);
+  return 0;
+}
+
+int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const float *d3, int n_rays, int nearest,
+                        const float *best_t, unsigned char *visited) {
+  if (!q10 || n_quadrics <= 0 || !visited) return -1;
+  std::vector<const float *> params;
+  for (int k = 0; k < n_quadrics; k++) params.push_back(q10 + 10 * (size_t)k);
+  QuadricIndex qi;
+  build_quadric_index(params, qi);
+  for (int r = 0; r < n_rays; r++) {
+    unsigned char *v = visited + (size_t)r * n_quadrics;
+    memset(v, 0, n_quadrics);
+    for (int k = qi.n_idx; k < n_quadrics; k++) v[qi.order[k]] = 1;       // not indexed: always scanned
+    if (!qi.n_idx) continue;
+    std::vector<int> stack(1, 0);
+    while (!stack.empty()) {
+      const int k = stack.back(); stack.pop_back();
+      const float4 mg = qi.marg[k];
+      const QIndexConsts qk = {mg.x, qi.behind_rel, mg.y, mg.z, mg.w};
+      if (qnode_prune(qi.bvh.node[k], P3[3 * r], P3[3 * r + 1], P3[3 * r + 2], d3[3 * r], d3[3 * r + 1], d3[3 * r + 2],
+                      nearest != 0, nearest ? best_t[r] : 0.0f, qk)) continue;
+      const int2 kid = qi.bvh.kids[k];
+      if (kid.x >= 0) { stack.push_back(kid.y & 0x0fffffff); stack.push_back(kid.x); }
+      else for (int i = 0; i < kid.y; i++) v[qi.order[-kid.x - 1 + i]] = 1;   // slot -kid.x-1+i holds input quadric order[slot]
+    }
+  }
+  return qi.n_idx;
+}
+
 int rt_set_accel(int mode) {
   if (mode != 0 && mode != 1) return set_err(RT_ERR_ARG, "rt_set_accel: mode must be 0 or 1");
   g_accel = mode;
@@ -485,7 +582,7 @@ int rt_scene_upload(const rt_scene *scene) {
   std::vector<float4> sph, sph_hot, sph_prim, pln, quad, quad_hot, quad_prim, mat(2 * (size_t)n + 1), lights(4 * (size_t)nl + 1);
   std::vector<int> sph_idx, pln_idx, quad_idx;
   std::vector<int2> slot((size_t)n + 1);
-  std::vector<int> sphere_order;
+  std::vector<int> sphere_order, quad_order;
   for (int i = 0; i < n; i++) {
     const rt_shape &s = scene->shapes[i];
     // opacity, C/raycast.c:383: 1.0 - reflectivity - refractivity in double, stored float
@@ -500,23 +597,7 @@ int rt_scene_upload(const rt_scene *scene) {
       pln.push_back(make_float4(s.params[0], s.params[1], s.params[2], 0.f));
       pln_idx.push_back(i);
     } else if (s.type == RT_QUADRIC) {
-      slot[i] = make_int2(2, (int)quad_idx.size());
-      quad.push_back(make_float4(s.params[0], s.params[1], s.params[2], s.params[3]));
-      quad.push_back(make_float4(s.params[4], s.params[5], s.params[6], s.params[7]));
-      quad.push_back(make_float4(s.params[8], s.params[9], 0.f, 0.f));
-      {
-        const float *q = s.params;
-        const float S2 = fabsf(q[0]) + fabsf(q[1]) + fabsf(q[2]) + fabsf(q[3]) + fabsf(q[4]) + fabsf(q[5]);
-        const float S1 = fabsf(q[6]) + fabsf(q[7]) + fabsf(q[8]);
-        const float4 h0 = make_float4(q[0], q[1], q[2], q[3]), h1 = make_float4(q[4], q[5], q[6], q[7]),
-                     h2 = make_float4(q[8], q[9], S2 * 1.000001f, S1 * 1.000001f);
-        quad_hot.push_back(h0); quad_hot.push_back(h1); quad_hot.push_back(h2);
-        const QuadFilter f = quad_filter_setup(h0, h1, h2, 0.0f, 0.0f, 0.0f);
-        quad_prim.push_back(make_float4(f.As, f.Bs, f.Cs, f.Ds));
-        quad_prim.push_back(make_float4(f.Es, f.Fs, f.m0, f.eb));
-        quad_prim.push_back(make_float4(f.gx, f.gy, f.gz, 0.f));
-      }
-      quad_idx.push_back(i);
+      quad_order.push_back(i);                                 // laid out below, once the index is decided
     } else {
       return set_err(RT_ERR_ARG, "shape %d has unknown type %d", i, s.type);
     }
@@ -584,7 +665,6 @@ int rt_scene_upload(const rt_scene *scene) {
   }
   // pad the per-sphere arrays to a multiple of 4 with entries the reject filter never passes
   // (r*r = -inf => k = -inf) so the hot loops can run unrolled without a tail
-  for (int k = 0; k < 3; k++) quad_hot.push_back(make_float4(0.f, 0.f, 0.f, 0.f));   // prefetch spare
   const size_t padded = (sph_hot.size() + 3) / 4 * 4 + 4;   // + one prefetch group
   while (sph_hot.size() < padded) {
     sph_hot.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));
@@ -596,11 +676,44 @@ int rt_scene_upload(const rt_scene *scene) {
   // light buffer (opt-in: rt_set_accel(1) or RT_ACCEL=1)
   LightBuffer lb;
   const bool have_lb = have_bvh && nl > 0 && n_sph_real > 0 && build_light_buffer(scene, sph, n_sph_real, lb);
+  // Quadrics: file order; in accel mode the ellipsoids the index can certify (rt_qindex.cuh) come first, in
+  // the leaf order of their own bounding-sphere hierarchy.  Any order is parity-safe, as for the spheres.
+  QuadricIndex qi;
+  if (have_lb && !quad_order.empty() && !getenv("RT_NO_QINDEX")) {
+    std::vector<const float *> params;
+    for (int i : quad_order) params.push_back(scene->shapes[i].params);
+    build_quadric_index(params, qi);
+    std::vector<int> reordered;
+    for (int k : qi.order) reordered.push_back(quad_order[k]);
+    quad_order.swap(reordered);
+  }
+  const int n_qidx = qi.n_idx;
+  const SphereBvh &qbvh = qi.bvh;
+  const std::vector<float4> &qbvh_marg = qi.marg;
+  const float q_behind_rel = qi.behind_rel;
+  for (int i : quad_order) {
+    const float *q = scene->shapes[i].params;
+    slot[i] = make_int2(2, (int)quad_idx.size());
+    quad.push_back(make_float4(q[0], q[1], q[2], q[3]));
+    quad.push_back(make_float4(q[4], q[5], q[6], q[7]));
+    quad.push_back(make_float4(q[8], q[9], 0.f, 0.f));
+    const float S2 = fabsf(q[0]) + fabsf(q[1]) + fabsf(q[2]) + fabsf(q[3]) + fabsf(q[4]) + fabsf(q[5]);
+    const float S1 = fabsf(q[6]) + fabsf(q[7]) + fabsf(q[8]);
+    const float4 h0 = make_float4(q[0], q[1], q[2], q[3]), h1 = make_float4(q[4], q[5], q[6], q[7]),
+                 h2 = make_float4(q[8], q[9], S2 * 1.000001f, S1 * 1.000001f);
+    quad_hot.push_back(h0); quad_hot.push_back(h1); quad_hot.push_back(h2);
+    const QuadFilter f = quad_filter_setup(h0, h1, h2, 0.0f, 0.0f, 0.0f);
+    quad_prim.push_back(make_float4(f.As, f.Bs, f.Cs, f.Ds));
+    quad_prim.push_back(make_float4(f.Es, f.Fs, f.m0, f.eb));
+    quad_prim.push_back(make_float4(f.gx, f.gy, f.gz, 0.f));
+    quad_idx.push_back(i);
+  }
+  for (int k = 0; k < 3; k++) quad_hot.push_back(make_float4(0.f, 0.f, 0.f, 0.f));   // prefetch spare
   // one blob, 256-byte aligned sections
   struct Sec { const void *src; size_t bytes; size_t off; };
   std::vector<float4> lb_hot;
   if (have_lb) { lb_hot.resize(lb.items.size()); for (size_t k = 0; k + 1 < lb.items.size(); k++) lb_hot[k] = sph_hot[lb.items[k]]; }
-  Sec secs[19] = {
+  Sec secs[22] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
@@ -611,7 +724,9 @@ int rt_scene_upload(const rt_scene *scene) {
       {lb.start.data(), have_lb ? lb.start.size() * 4 : 0, 0}, {lb.items.data(), have_lb ? lb.items.size() * 4 : 0, 0},
       {lb.caps.data(), have_lb ? lb.caps.size() * 4 : 0, 0},
       {bvh.node.data(), have_lb ? bvh.node.size() * 16 : 0, 0}, {bvh.kids.data(), have_lb ? bvh.kids.size() * 8 : 0, 0},
-      {lb_hot.data(), have_lb ? lb_hot.size() * 16 : 0, 0}};
+      {lb_hot.data(), have_lb ? lb_hot.size() * 16 : 0, 0},
+      {qbvh.node.data(), n_qidx ? qbvh.node.size() * 16 : 0, 0}, {qbvh.kids.data(), n_qidx ? qbvh.kids.size() * 8 : 0, 0},
+      {qbvh_marg.data(), n_qidx ? qbvh_marg.size() * 16 : 0, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -644,6 +759,11 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.bvh_node = have_lb ? (const float4 *)(b + secs[16].off) : nullptr;
     sc.bvh_kids = have_lb ? (const int2 *)(b + secs[17].off) : nullptr;
     sc.lb_hot = have_lb ? (const float4 *)(b + secs[18].off) : nullptr;
+    sc.qbvh_node = n_qidx ? (const float4 *)(b + secs[19].off) : nullptr;
+    sc.qbvh_kids = n_qidx ? (const int2 *)(b + secs[20].off) : nullptr;
+    sc.qbvh_marg = n_qidx ? (const float4 *)(b + secs[21].off) : nullptr;
+    sc.n_qidx = n_qidx;
+    sc.q_behind_rel = q_behind_rel;
   }
   g_have_scene = true;
   g_n_lights = nl;

@@ -123,6 +123,9 @@ RT_DEV void finish_hit(const DevScene &sc, v3 o, v3 d, float t, int idx, v3 &P, 
 template <bool ANY>
 RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_sph, float &best_t, int &best_idx,
                       unsigned &n_cand, unsigned &n_tests);
+template <bool ANY, bool ZRULE>
+__device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj, float &best_t, int &best_idx,
+                                        unsigned &n_cand, unsigned &n_tests);
 #define RT_PRIM_PX_BRUTE 4   // pixels (= primary rays) per thread: one sphere load feeds four reject tests
 template <bool ACCEL>
 __global__ void __launch_bounds__(256)
@@ -215,7 +218,21 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
     n_pln += (unsigned long long)sc.n_planes * n_live;
     // quadrics: the origin is (0,0,0), so the filter's origin-only part is a per-quadric
     // constant prepared on the host (quad_prim); survivors take the reference's expression tree
-    for (int kq = 0; kq < sc.n_quadrics; kq++) {
+    int kq0 = 0;
+    if constexpr (ACCEL) {
+      // indexed ellipsoids through their hierarchy; the rest below
+      if (sc.n_qidx > 0) {
+        kq0 = sc.n_qidx;
+        #pragma unroll 1
+        for (int k = 0; k < RT_PRIM_PX; k++) {
+          if (!((live >> k) & 1u)) continue;
+          unsigned nt = 0, nc = 0;
+          qbvh_trace<false, false>(sc, o, d[k], -1, best_t[k], best_idx[k], nc, nt);
+          n_cand += nc; n_quad += nt;
+        }
+      }
+    }
+    for (int kq = kq0; kq < sc.n_quadrics; kq++) {
       const float4 p0 = sc.quad_prim[3 * kq], p1 = sc.quad_prim[3 * kq + 1], p2 = sc.quad_prim[3 * kq + 2];
       QuadFilter f;
       f.As = p0.x; f.Bs = p0.y; f.Cs = p0.z; f.Ds = p0.w; f.Es = p1.x; f.Fs = p1.y; f.m0 = p1.z; f.eb = p1.w;
@@ -238,7 +255,7 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
         }
       }
     }
-    n_quad += (unsigned long long)sc.n_quadrics * n_live;
+    n_quad += (unsigned long long)(sc.n_quadrics - kq0) * n_live;
     #pragma unroll
     for (int k = 0; k < RT_PRIM_PX; k++) {
       const int i = base + k * blockDim.x;
@@ -544,6 +561,51 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_
   return false;
 }
 
+// Traversal of the hierarchy over the indexed ellipsoids (quadric slots 0 .. n_qidx-1, rt_qindex.cuh) for one
+// ray; what a leaf lets through takes the same chain as resolve_quadrics: reject filter, then the reference's
+// expression tree.  ZRULE: the hit-point rule of C/raycast.c:492-494
+// (every ray but the primary ones).  ANY = true: shadow query, returns at the first hit.
+template <bool ANY, bool ZRULE>
+__device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj, float &best_t, int &best_idx,
+                                        unsigned &n_cand, unsigned &n_tests) {
+  int stack[32];
+  int sp = 0;
+  stack[sp++] = 0;
+  while (sp > 0) {
+    const int k = stack[--sp];
+    const float4 mg = sc.qbvh_marg[k];
+    const QIndexConsts qk = {mg.x, sc.q_behind_rel, mg.y, mg.z, mg.w};
+    if (qnode_prune(sc.qbvh_node[k], P.x, P.y, P.z, d.x, d.y, d.z, !ANY, best_t, qk)) continue;
+    const int2 kid = sc.qbvh_kids[k];
+    if (kid.x >= 0) {
+      const int axis = kid.y >> 28, right = kid.y & 0x0fffffff;
+      const float da = axis == 0 ? d.x : axis == 1 ? d.y : d.z;
+      const bool left_first = da >= 0.0f;
+      stack[sp++] = left_first ? right : kid.x;                // depth <= 28 (host), one net entry per level
+      stack[sp++] = left_first ? kid.x : right;
+    } else {
+      const int first = -kid.x - 1;
+      for (int i = 0; i < kid.y; i++) {
+        const int kk = first + i;                              // leaves are runs of consecutive quadric slots
+        n_tests++;
+        const int idx = sc.quad_idx[kk];
+        if (idx == obj) continue;                              // C/raycast.c:450
+        const QuadFilter f = quad_filter_setup(sc.quad_hot[3 * kk], sc.quad_hot[3 * kk + 1], sc.quad_hot[3 * kk + 2], P.x, P.y, P.z);
+        if (!(quad_filter_v(f, d) >= 0.0f)) continue;
+        const quad10 qq = load_quad(sc.quad, kk);
+        const float c_q = (float)quadric_cq(P, qq);
+        float t;
+        n_cand++;
+        if (!quadric_t(P, d, qq, c_q, t)) continue;
+        if (ZRULE && add32(P.z, mul32(t, d.z)) < P.z) continue;
+        if (ANY) { if (t > 0.0f && t < RT_INF) return true; }
+        else if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
+      }
+    }
+  }
+  return false;
+}
+
 // Scan variants: the bundle scans are compiled for NR, NR-2, NR-4, ... >= 3 ray slots; a warp runs
 // the smallest one that holds the largest number of rays any of its hit points still has alive.
 template <int NRV, int NRMIN>
@@ -582,7 +644,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
   // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
   // counters are products of these with the scene's primitive counts, formed at the end
   unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_ls = 0, n_cand = 0;
-  unsigned d_sph = 0, d_pln = 0, d_quad = 0, d_slots = 0, o_sph = 0;   // direction tests executed: live ray slots x primitives scanned with them
+  unsigned d_sph = 0, d_pln = 0, d_quad = 0, d_slots = 0, o_sph = 0, o_quad = 0;   // direction tests executed: live ray slots x primitives scanned with them
   // Dynamic scheduling: every warp claims 32 consecutive entries of one class list at a time
   // (heaviest class first), so no SM idles while another still holds a backlog, and the hit
   // points a warp shades together need about the same number of ray slots.
@@ -769,13 +831,37 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
         repack();
       }
       // ---- quadrics --------------------------------------------------------------
-      if constexpr (QUADS)
-      for (int cs = 0; cs < sc.n_quadrics; cs += RT_CHUNK) {
-        const int n = min(RT_CHUNK, sc.n_quadrics - cs);
-        d_quad += (unsigned)__popc(alive) * (unsigned)n;
-        d_slots += (unsigned)nrv * (unsigned)n;
-        scan_quadrics_v<NR, VMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
-        if (nrv > VMIN) repack();
+      if constexpr (QUADS) {
+        int q0 = 0;
+        if constexpr (ACCEL) {
+          // indexed ellipsoids through their hierarchy (rt_qindex.cuh); every other quadric is scanned below
+          if (sc.n_qidx > 0) {
+            q0 = sc.n_qidx;
+            for (unsigned m = alive & ~(r_on ? 1u : 0u); m; m &= m - 1) {
+              const int j = __ffs(m) - 1;
+              const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+              unsigned nt = 0;
+              float bt = RT_INF;
+              int bi = -1;
+              if (qbvh_trace<true, true>(sc, P, dj, obj, bt, bi, n_cand, nt)) alive &= ~(1u << j);
+              d_quad += nt; o_quad += nt;
+            }
+            if (r_on) {
+              unsigned nt = 0;
+              qbvh_trace<false, true>(sc, P, rd, obj, best_t, best_idx, n_cand, nt);
+              d_quad += nt; o_quad += nt; d_slots += nt;
+            }
+            repack();
+          }
+        }
+        for (int cs = q0; cs < sc.n_quadrics; cs += RT_CHUNK) {
+          const int n = min(RT_CHUNK, sc.n_quadrics - cs);
+          d_quad += (unsigned)__popc(alive) * (unsigned)n;
+          d_slots += (unsigned)nrv * (unsigned)n;
+          o_quad += (unsigned)n;
+          scan_quadrics_v<NR, VMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+          if (nrv > VMIN) repack();
+        }
       }
       // ---- Phong for the lights of this pass that stayed unoccluded, in light order
       for (unsigned m = alive & ~(r_on ? 1u : 0u); m; m &= m - 1) {
@@ -832,22 +918,20 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
                  hit_class(sc, P2, N2, best_idx, level + 1 < sc.max_depth - 1, NR));
     }
   }
-  unsigned v[11] = {n_refl, n_lit, n_hp, n_pass_sum, d_sph, n_ls, n_cand, d_pln, d_quad, d_slots, o_sph};
+  unsigned v[12] = {n_refl, n_lit, n_hp, n_pass_sum, d_sph, n_ls, n_cand, d_pln, d_quad, d_slots, o_sph, o_quad};
   #pragma unroll
-  for (int k = 0; k < 11; k++) {
+  for (int k = 0; k < 12; k++) {
     #pragma unroll
     for (int off = 16; off; off >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
   }
   if ((threadIdx.x & 31) == 0) {
     typedef unsigned long long u64;
-    const u64 np = sc.n_planes, nq = sc.n_quadrics;
+    const u64 np = sc.n_planes;
     if (v[0]) atomicAdd(&counters[CT_RAYS_REFLECTION], (u64)v[0]);
     if (v[1]) atomicAdd(&counters[CT_RAYS_SHADOW], (u64)v[1] * sc.n_lights);
     if (v[2]) atomicAdd(&counters[CT_HIT_POINTS], (u64)v[2]);
-    if (v[3]) {
-      if (np) atomicAdd(&counters[CT_PLN_O], v[3] * np);
-      if (nq) atomicAdd(&counters[CT_QUAD_O], v[3] * nq);
-    }
+    if (v[3] && np) atomicAdd(&counters[CT_PLN_O], v[3] * np);
+    if (v[11]) atomicAdd(&counters[CT_QUAD_O], (u64)v[11]);
     if (v[4]) atomicAdd(&counters[CT_SPH_D], (u64)v[4]);
     if (v[7]) atomicAdd(&counters[CT_PLN_D], (u64)v[7]);
     if (v[8]) atomicAdd(&counters[CT_QUAD_D], (u64)v[8]);

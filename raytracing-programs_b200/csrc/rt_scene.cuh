@@ -6,6 +6,7 @@
 // (C/raycast.c:450,456).
 #pragma once
 #include "rt_math.cuh"
+#include "rt_qindex.cuh"
 
 #define RT_MAX_DEPTH_CAP 64
 struct DevScene {
@@ -38,6 +39,14 @@ struct DevScene {
   // (in this mode the host lays the spheres out in leaf order).
   const float4 *bvh_node;
   const int2 *bvh_kids;
+  // The same kind of hierarchy over the ellipsoids among the quadrics (rt_qindex.cuh): they take quadric slots
+  // 0 .. n_qidx-1 in leaf order, every other quadric follows and is scanned as before.  qbvh_node = NULL or
+  // n_qidx = 0: no quadric index.
+  const float4 *qbvh_node;
+  const int2 *qbvh_kids;
+  const float4 *qbvh_marg;  // per node {miss_rel, behind_abs, t_rel, t_abs}: the largest margins its members need
+  int n_qidx;
+  float q_behind_rel;
 };
 #define RT_LB_RES 32
 #define RT_LB_LEVELS 6

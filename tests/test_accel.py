@@ -48,6 +48,7 @@ def test_accel_on_synthetic_scenes(renderer, scene, W, H):
     assert np.array_equal(a, b), rtlib.compare(a, b)
     assert sa.rays == sb.rays                                   # same rays of the reference semantics
     assert sb.sphere_tests_d < sa.sphere_tests_d                # fewer tests executed for them
+    assert sb.quadric_tests_d <= sa.quadric_tests_d
     assert np.array_equal(b, rtlib.oracle_render(scene, W, H))
 
 
@@ -74,6 +75,70 @@ def test_accel_far_hit_points_fall_back(renderer, tmp_path):
     assert np.array_equal(a, b), rtlib.compare(a, b)
     assert np.array_equal(b, rtlib.oracle_render(str(p), 640, 384))
     assert a.max() > 0
+
+
+def _ellipsoid_line(rng, centre, axes, rotate, refl):
+    R = np.eye(3)
+    if rotate:
+        R, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+    s = rng.uniform(0.5, 6.0)
+    M = s * (R @ np.diag(1.0 / np.asarray(axes) ** 2) @ R.T)
+    g = -2.0 * M @ centre
+    j = centre @ M @ centre - s
+    co = dict(a=M[0, 0], b=M[1, 1], c=M[2, 2], d=2 * M[0, 1], e=2 * M[0, 2], f=2 * M[1, 2], g=g[0], h=g[1], i=g[2], j=j)
+    col = rng.uniform(0.1, 1.0, 3)
+    return (f"quadric, diffuse_color: [{col[0]:.4f}, {col[1]:.4f}, {col[2]:.4f}], specular_color: [1, 1, 1], "
+            + ", ".join(f"{k}: {v:.9g}" for k, v in co.items()) + f", reflectivity: {refl:.2f}")
+
+
+@pytest.mark.timeout(900)
+def test_accel_quadric_index(renderer, tmp_path):
+    """The hierarchy over the ellipsoids among the quadrics (csrc/rt_qindex.cuh): rotated and axis-aligned ellipsoids
+    of mixed sizes, mirrors among them, quadrics the index cannot hold (cylinder, cone, paraboloid), a floor reaching
+    far out, a light next to one ellipsoid and one inside another."""
+    rng = np.random.default_rng(12)
+    lines = ["camera, width: 2, height: 1.3",
+             "plane, normal: [0, 1, 0.01], position: [0, -6, 0], diffuse_color: [0.7, 0.7, 0.7], specular_color: [1, 1, 1], reflectivity: 0.4",
+             "sphere, radius: 2, position: [3, 0, -22], diffuse_color: [1, 0.2, 0.2], specular_color: [1, 1, 1], reflectivity: 0.6, refractivity: 0, ior: 1",
+             "sphere, radius: 0.7, position: [-4, -2, -12], diffuse_color: [0.2, 1, 0.2], specular_color: [1, 1, 1], reflectivity: 0, refractivity: 0, ior: 1",
+             "quadric, diffuse_color: [0.9, 0.9, 0.2], specular_color: [1, 1, 1], a: 1, b: 0, c: 1, d: 0, e: 0, f: 0, g: 16, h: 0, i: 60, j: 963, reflectivity: 0.3",
+             "quadric, diffuse_color: [0.2, 0.9, 0.9], specular_color: [1, 1, 1], a: 1, b: -0.3, c: 1, d: 0, e: 0, f: 0, g: -20, h: 0, i: 50, j: 725, reflectivity: 0",
+             "quadric, diffuse_color: [0.9, 0.4, 0.9], specular_color: [1, 1, 1], a: 0.5, b: 0, c: 0.5, d: 0, e: 0, f: 0, g: 0, h: -1, i: 40, j: 795, reflectivity: 0.2"]
+    centres = []
+    for k in range(140):
+        c = np.array([rng.uniform(-18, 18), rng.uniform(-5, 10), -rng.uniform(8, 70)])
+        centres.append(c)
+        axes = rng.uniform(0.25, 1.6, 3) * (3.0 if k % 17 == 0 else 1.0)
+        lines.append(_ellipsoid_line(rng, c, axes, rotate=(k % 3 != 0), refl=[0, 0, 0.25, 0.5, 0.9][k % 5]))
+    lines += [f"light, color: [2, 2, 2], position: [{centres[3][0] + 1.9:.4f}, {centres[3][1] + 0.3:.4f}, {centres[3][2] + 0.2:.4f}], radial-a0: 1, radial-a1: 0, radial-a2: 0.002",
+              f"light, color: [1, 2, 1], position: [{centres[0][0]:.4f}, {centres[0][1]:.4f}, {centres[0][2]:.4f}], radial-a0: 1, radial-a1: 0, radial-a2: 0.002",
+              "light, color: [2, 1.5, 1], position: [-25, 30, -10], radial-a0: 1, radial-a1: 0, radial-a2: 0.0005",
+              "light, color: [1, 1, 2], position: [10, 12, 5], radial-a0: 1, radial-a1: 0, radial-a2: 0.0005"]
+    p = tmp_path / "ellipsoids.scene"
+    p.write_text("\n".join(lines) + "\n")
+    for W, H in ((480, 312), (257, 131)):
+        a, sa = render(renderer, str(p), W, H, 0)
+        b, sb = render(renderer, str(p), W, H, 1)
+        assert np.array_equal(a, b), rtlib.compare(a, b)
+        assert sa.rays == sb.rays
+        assert sb.quadric_tests_d * 3 < sa.quadric_tests_d          # the index does prune
+        assert np.array_equal(b, rtlib.oracle_render(str(p), W, H))
+    assert a.max() > 0 and len(np.unique(a)) > 50
+
+
+@pytest.mark.timeout(900)
+def test_accel_quadric_index_deep_bounces(renderer):
+    """C5 with the bounce limit of the reference's CUDA variant (50): long reflection chains between ellipsoids,
+    spheres and the tilted floors, accelerated frame = brute-force frame."""
+    scene = BIG[1][0]
+    renderer.set_max_depth(50)
+    try:
+        a, sa = render(renderer, scene, 192, 144, 0)
+        b, sb = render(renderer, scene, 192, 144, 1)
+    finally:
+        renderer.set_max_depth(7)
+    assert np.array_equal(a, b), rtlib.compare(a, b)
+    assert sa.rays == sb.rays and sb.quadric_tests_d * 5 < sa.quadric_tests_d
 
 
 @pytest.mark.timeout(900)
