@@ -265,17 +265,21 @@ bool build_sphere_bvh(const std::vector<float4> &sph, int n_sph, SphereBvh &out)
 // Index over the ellipsoids among a list of quadrics (rt_qindex.cuh).  order: positions of the input list, the
 // n_idx certified ellipsoids first in the leaf order of their bounding-sphere hierarchy, then everything else in
 // input order.  marg: per node {miss_rel, behind_abs, t_rel, t_abs}, the largest margins its members need.
+struct QLbItem { double K, lmin, a0, a1, a2, shift; };
 struct QuadricIndex {
   std::vector<int> order;
   int n_idx = 0;
   SphereBvh bvh;
   std::vector<float4> marg;
   float behind_rel = 0.f;
+  std::vector<float4> slot_ball;     // bounding sphere of indexed slot k (leaf order) and its level-set constants, for the light buffer
+  std::vector<QLbItem> slot_q;
 };
 
 void build_quadric_index(const std::vector<const float *> &params, QuadricIndex &out) {
   std::vector<int> idxd, rest;
   std::vector<float4> balls, marg;
+  std::vector<QLbItem> qits;
   out = QuadricIndex();
   for (size_t k = 0; k < params.size(); k++) {
     QIndexItem it;
@@ -285,12 +289,16 @@ void build_quadric_index(const std::vector<const float *> &params, QuadricIndex 
       idxd.push_back((int)k);
       balls.push_back(make_float4(it.centre[0], it.centre[1], it.centre[2], it.r_item));
       marg.push_back(make_float4(it.miss_rel, it.behind_abs, it.t_rel, it.t_abs));
+      {
+        const double sx = it.c[0] - it.centre[0], sy = it.c[1] - it.centre[1], sz = it.c[2] - it.centre[2];
+        qits.push_back(QLbItem{it.K, it.lmin, it.a0, it.a1, it.a2, sqrt(sx * sx + sy * sy + sz * sz)});
+      }
       out.behind_rel = std::max(out.behind_rel, it.behind_rel);
     } else rest.push_back((int)k);
   }
   if (idxd.size() >= 8 && build_sphere_bvh(balls, (int)balls.size(), out.bvh)) {
     out.n_idx = (int)idxd.size();
-    for (int k : out.bvh.items) out.order.push_back(idxd[k]);
+    for (int k : out.bvh.items) { out.order.push_back(idxd[k]); out.slot_ball.push_back(balls[k]); out.slot_q.push_back(qits[k]); }
     out.order.insert(out.order.end(), rest.begin(), rest.end());
     // children are created after their parent, so one backward sweep folds the members' margins upwards
     auto fold = [](float4 x, float4 y) { return make_float4(std::max(x.x, y.x), std::max(x.y, y.y), std::max(x.z, y.z), std::max(x.w, y.w)); };
@@ -308,7 +316,11 @@ void build_quadric_index(const std::vector<const float *> &params, QuadricIndex 
   }
 }
 
-bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, int n_sph, LightBuffer &lb) {
+// qit = NULL: the items are spheres (inflation of the reject-filter contract, above).  qit != NULL: the items are
+// indexed ellipsoids (rt_qindex.cuh): the reference can only report ellipsoid s if the line enters {q <= delta(|P - c|)},
+// which lies within sqrt((K + a0 + a1 s + a2 s^2)/lmin) of the centre, s = |P - c| <= Dcap + |c - L|; only the four
+// nearest distance levels are built for them (farther out the inflated ellipsoids fill too many cells: hierarchy).
+bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, int n_sph, const std::vector<QLbItem> *qit, LightBuffer &lb) {
   const int R = RT_LB_RES, CELLS = 6 * R * R, nl = scene->num_lights;
   std::vector<double> cb(3 * (size_t)CELLS), cbeta(CELLS), ccos(CELLS), csin(CELLS);
   for (int face = 0; face < 6; face++)
@@ -366,12 +378,18 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
     for (int lv = 0; lv < RT_LB_LEVELS; lv++) {
       const double Dcap = Rl * mult[lv];
       capf[lv] = (float)((Dcap * (1.0 - 1e-3)) * (Dcap * (1.0 - 1e-3)));
+      if (qit && lv >= 4) { capf[lv] = -1.f; continue; }
       auto &pv = pairs[(size_t)l * RT_LB_LEVELS + lv];
       for (int s = 0; s < n_sph; s++) {
         const double dx = sph[s].x - L[0], dy = sph[s].y - L[1], dz = sph[s].z - L[2], r = fabs((double)sph[s].w);
         const double dist = sqrt(dx * dx + dy * dy + dz * dz);
         const double Tcap = (Dcap + dist) * (Dcap + dist);
-        const double reff = sqrt(r * r + ldexp(1.0, -18) * (Tcap + r * r)) + ldexp(8.0, -24) * sqrt(Tcap);
+        double reff = sqrt(r * r + ldexp(1.0, -18) * (Tcap + r * r)) + ldexp(8.0, -24) * sqrt(Tcap);
+        if (qit) {
+          const QLbItem &e = (*qit)[s];
+          const double sm = Dcap + dist + 2.0 * e.shift;
+          reff = (sqrt((e.K + e.a0 + e.a1 * sm + e.a2 * sm * sm) / e.lmin) + e.shift) * (1.0 + 1e-6) + 1e-7 * sm;
+        }
         const bool all = !(dist > reff * (1.0 + 1e-6)) || !std::isfinite(reff);
         double a[3] = {0, 0, 0}, theta = 4.0;
         if (!all) { a[0] = dx / dist; a[1] = dy / dist; a[2] = dz / dist; theta = asin(std::min(1.0, reff / dist)) + 3e-4; }
@@ -675,7 +693,7 @@ int rt_scene_upload(const rt_scene *scene) {
   const int n_sph_real = (int)slot_count_spheres;
   // light buffer (opt-in: rt_set_accel(1) or RT_ACCEL=1)
   LightBuffer lb;
-  const bool have_lb = have_bvh && nl > 0 && n_sph_real > 0 && build_light_buffer(scene, sph, n_sph_real, lb);
+  const bool have_lb = have_bvh && nl > 0 && n_sph_real > 0 && build_light_buffer(scene, sph, n_sph_real, nullptr, lb);
   // Quadrics: file order; in accel mode the ellipsoids the index can certify (rt_qindex.cuh) come first, in
   // the leaf order of their own bounding-sphere hierarchy.  Any order is parity-safe, as for the spheres.
   QuadricIndex qi;
@@ -688,6 +706,8 @@ int rt_scene_upload(const rt_scene *scene) {
     quad_order.swap(reordered);
   }
   const int n_qidx = qi.n_idx;
+  LightBuffer lbq;                        // the same cube maps over the indexed ellipsoids
+  const bool have_lbq = n_qidx > 0 && !getenv("RT_NO_QLB") && build_light_buffer(scene, qi.slot_ball, n_qidx, &qi.slot_q, lbq);
   const SphereBvh &qbvh = qi.bvh;
   const std::vector<float4> &qbvh_marg = qi.marg;
   const float q_behind_rel = qi.behind_rel;
@@ -713,7 +733,7 @@ int rt_scene_upload(const rt_scene *scene) {
   struct Sec { const void *src; size_t bytes; size_t off; };
   std::vector<float4> lb_hot;
   if (have_lb) { lb_hot.resize(lb.items.size()); for (size_t k = 0; k + 1 < lb.items.size(); k++) lb_hot[k] = sph_hot[lb.items[k]]; }
-  Sec secs[22] = {
+  Sec secs[25] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
@@ -726,7 +746,9 @@ int rt_scene_upload(const rt_scene *scene) {
       {bvh.node.data(), have_lb ? bvh.node.size() * 16 : 0, 0}, {bvh.kids.data(), have_lb ? bvh.kids.size() * 8 : 0, 0},
       {lb_hot.data(), have_lb ? lb_hot.size() * 16 : 0, 0},
       {qbvh.node.data(), n_qidx ? qbvh.node.size() * 16 : 0, 0}, {qbvh.kids.data(), n_qidx ? qbvh.kids.size() * 8 : 0, 0},
-      {qbvh_marg.data(), n_qidx ? qbvh_marg.size() * 16 : 0, 0}};
+      {qbvh_marg.data(), n_qidx ? qbvh_marg.size() * 16 : 0, 0},
+      {lbq.start.data(), have_lbq ? lbq.start.size() * 4 : 0, 0}, {lbq.items.data(), have_lbq ? lbq.items.size() * 4 : 0, 0},
+      {lbq.caps.data(), have_lbq ? lbq.caps.size() * 4 : 0, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -762,9 +784,16 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.qbvh_node = n_qidx ? (const float4 *)(b + secs[19].off) : nullptr;
     sc.qbvh_kids = n_qidx ? (const int2 *)(b + secs[20].off) : nullptr;
     sc.qbvh_marg = n_qidx ? (const float4 *)(b + secs[21].off) : nullptr;
+    sc.lbq_start = have_lbq ? (const unsigned *)(b + secs[22].off) : nullptr;
+    sc.lbq_items = have_lbq ? (const int *)(b + secs[23].off) : nullptr;
+    sc.lbq_caps = have_lbq ? (const float *)(b + secs[24].off) : nullptr;
     sc.n_qidx = n_qidx;
     sc.q_behind_rel = q_behind_rel;
   }
+  if (getenv("RT_VERBOSE"))
+    fprintf(stderr, "rt_scene_upload: %d spheres, %d planes, %d quadrics (%d indexed), light buffer %s (%zu items), ellipsoid light buffer %s (%zu items), blob %zu bytes\n",
+            n_sph_real, (int)pln_idx.size(), (int)quad_idx.size(), n_qidx, have_lb ? "yes" : "no", have_lb ? lb.items.size() : (size_t)0,
+            have_lbq ? "yes" : "no", have_lbq ? lbq.items.size() : (size_t)0, total);
   g_have_scene = true;
   g_n_lights = nl;
   g_n_shapes = n;

@@ -565,6 +565,21 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_
 // ray; what a leaf lets through takes the same chain as resolve_quadrics: reject filter, then the reference's
 // expression tree.  ZRULE: the hit-point rule of C/raycast.c:492-494
 // (every ray but the primary ones).  ANY = true: shadow query, returns at the first hit.
+// One ray against quadric slot kk, the chain of resolve_quadrics: reject filter, then the reference's expression
+// tree and (ZRULE) the hit-point rule of C/raycast.c:492-494.  Returns whether the reference reports a t; the
+// caller applies its own acceptance (0 < t < inf for a shadow ray, better_hit for a nearest-hit search).
+template <bool ZRULE>
+RT_DEV bool quadric_reported(const DevScene &sc, const v3 P, const v3 d, const int kk, float &t, unsigned &n_cand) {
+  const QuadFilter f = quad_filter_setup(sc.quad_hot[3 * kk], sc.quad_hot[3 * kk + 1], sc.quad_hot[3 * kk + 2], P.x, P.y, P.z);
+  if (!(quad_filter_v(f, d) >= 0.0f)) return false;
+  const quad10 qq = load_quad(sc.quad, kk);
+  const float c_q = (float)quadric_cq(P, qq);
+  n_cand++;
+  if (!quadric_t(P, d, qq, c_q, t)) return false;
+  if (ZRULE && add32(P.z, mul32(t, d.z)) < P.z) return false;
+  return true;
+}
+
 template <bool ANY, bool ZRULE>
 __device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj, float &best_t, int &best_idx,
                                         unsigned &n_cand, unsigned &n_tests) {
@@ -590,14 +605,8 @@ __device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3
         n_tests++;
         const int idx = sc.quad_idx[kk];
         if (idx == obj) continue;                              // C/raycast.c:450
-        const QuadFilter f = quad_filter_setup(sc.quad_hot[3 * kk], sc.quad_hot[3 * kk + 1], sc.quad_hot[3 * kk + 2], P.x, P.y, P.z);
-        if (!(quad_filter_v(f, d) >= 0.0f)) continue;
-        const quad10 qq = load_quad(sc.quad, kk);
-        const float c_q = (float)quadric_cq(P, qq);
         float t;
-        n_cand++;
-        if (!quadric_t(P, d, qq, c_q, t)) continue;
-        if (ZRULE && add32(P.z, mul32(t, d.z)) < P.z) continue;
+        if (!quadric_reported<ZRULE>(sc, P, d, kk, t, n_cand)) continue;
         if (ANY) { if (t > 0.0f && t < RT_INF) return true; }
         else if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
       }
@@ -841,9 +850,35 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
               const int j = __ffs(m) - 1;
               const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
               unsigned nt = 0;
-              float bt = RT_INF;
-              int bi = -1;
-              if (qbvh_trace<true, true>(sc, P, dj, obj, bt, bi, n_cand, nt)) alive &= ~(1u << j);
+              bool occl = false;
+              int lv = -1, cell = -1;
+              if (sc.lbq_start != nullptr) {
+                // the ellipsoids listed in the cell of the light's cube map that the direction from the light to P
+                // falls in (level by |P - L|), as for the spheres
+                const int l = pass * LB + (int)((lmap >> (4 * (j - (r_on ? 1 : 0)))) & 15ull);
+                const float4 lp = sc.lights[4 * l];
+                const float wx = lp.x - P.x, wy = lp.y - P.y, wz = lp.z - P.z;
+                const float q = __fmaf_rn(wz, wz, __fmaf_rn(wy, wy, wx * wx));
+                #pragma unroll
+                for (int v = RT_LB_LEVELS - 1; v >= 0; v--) lv = q <= sc.lbq_caps[l * RT_LB_LEVELS + v] ? v : lv;
+                cell = lb_cell(-dj.x, -dj.y, -dj.z);
+                if (lv >= 0 && cell >= 0) {
+                  const unsigned *st = sc.lbq_start + ((size_t)(l * RT_LB_LEVELS + lv) * 6 * RT_LB_RES * RT_LB_RES + cell);
+                  const unsigned k1 = st[1];
+                  for (unsigned k = st[0]; k < k1 && !occl; k++) {
+                    const int kk = sc.lbq_items[k];
+                    nt++;
+                    float t;
+                    if (sc.quad_idx[kk] != obj && quadric_reported<true>(sc, P, dj, kk, t, n_cand)) occl = t > 0.0f && t < RT_INF;   // C/raycast.c:450
+                  }
+                }
+              }
+              if (!(lv >= 0 && cell >= 0)) {
+                float bt = RT_INF;
+                int bi = -1;
+                occl = qbvh_trace<true, true>(sc, P, dj, obj, bt, bi, n_cand, nt);
+              }
+              if (occl) alive &= ~(1u << j);
               d_quad += nt; o_quad += nt;
             }
             if (r_on) {

@@ -47,6 +47,11 @@ struct DevScene {
   const float4 *qbvh_marg;  // per node {miss_rel, behind_abs, t_rel, t_abs}: the largest margins its members need
   int n_qidx;
   float q_behind_rel;
+  // Light buffer over the indexed ellipsoids (same layout as lb_*; items are quadric slots); NULL: shadow rays walk
+  // the hierarchy instead.
+  const unsigned *lbq_start;
+  const int *lbq_items;
+  const float *lbq_caps;
 };
 #define RT_LB_RES 32
 #define RT_LB_LEVELS 6
