@@ -152,6 +152,7 @@ int rt_dbg_qindex_prune(const float *node4, const float *P3, const float *d3, in
  * Returns the number of indexed quadrics, -1 on bad arguments. */
 int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const float *d3, int n_rays, int nearest,
                         const float *best_t, unsigned char *visited);
+long long rt_dbg_qindex_last_nodes(void);   /* hierarchy nodes tested by the last rt_dbg_qindex_visit call */
 
 /* Flatten to type-sorted SoA (+ original index) and upload to every device in use.
  * Takes the place of the list->VLA copy at C/raycast.c:87-107. The scene is copied;

@@ -235,18 +235,51 @@ bool bvh_build_rec(const std::vector<float4> &sph, std::vector<int> &ids, int lo
     for (int k = lo; k < hi; k++) out.items.push_back(ids[k]);
     return true;
   }
-  int axis = 0;
-  double ext = -1;
-  for (int a = 0; a < 3; a++) {
-    double cmn = 1e300, cmx = -1e300;
-    for (int k = lo; k < hi; k++) { const float4 &q = sph[ids[k]]; const double v = a == 0 ? q.x : a == 1 ? q.y : q.z; cmn = std::min(cmn, v); cmx = std::max(cmx, v); }
-    if (cmx - cmn > ext) { ext = cmx - cmn; axis = a; }
+  // Split: sweep the members sorted by centre along each axis and take the cut that minimises
+  // n_left * d_left^2 + n_right * d_right^2, d = diagonal of the side's bounding box (a node sphere is built around
+  // that box, and the chance that a ray meets it grows with its cross-section).  Deep down a lopsided tree falls back
+  // to the median along the widest axis, so the depth stays bounded.
+  int axis = 0, mid = (lo + hi) / 2;
+  const int n = hi - lo;
+  if (depth < 14 && !getenv("RT_BVH_MEDIAN")) {
+    double best = 1e300;
+    std::vector<int> tmp(ids.begin() + lo, ids.begin() + hi), keep;
+    std::vector<double> suf((size_t)n + 1);
+    for (int a = 0; a < 3; a++) {
+      std::sort(tmp.begin(), tmp.end(), [&](int x, int y) {
+        const float vx = a == 0 ? sph[x].x : a == 1 ? sph[x].y : sph[x].z, vy = a == 0 ? sph[y].x : a == 1 ? sph[y].y : sph[y].z;
+        return vx < vy || (vx == vy && x < y);
+      });
+      double bmn[3] = {1e300, 1e300, 1e300}, bmx[3] = {-1e300, -1e300, -1e300};
+      auto grow = [&](int id) {
+        const float4 &q = sph[id];
+        const double c[3] = {q.x, q.y, q.z}, r = fabs((double)q.w);
+        for (int k = 0; k < 3; k++) { bmn[k] = std::min(bmn[k], c[k] - r); bmx[k] = std::max(bmx[k], c[k] + r); }
+      };
+      auto diag2 = [&]() { return (bmx[0] - bmn[0]) * (bmx[0] - bmn[0]) + (bmx[1] - bmn[1]) * (bmx[1] - bmn[1]) + (bmx[2] - bmn[2]) * (bmx[2] - bmn[2]); };
+      for (int k = n - 1; k >= 1; k--) { grow(tmp[k]); suf[k] = diag2() * (n - k); }
+      for (int k = 0; k < 3; k++) { bmn[k] = 1e300; bmx[k] = -1e300; }
+      bool took = false;
+      for (int k = 1; k < n; k++) {
+        grow(tmp[k - 1]);
+        const double cost = diag2() * k + suf[k];
+        if (cost < best) { best = cost; axis = a; mid = lo + k; took = true; }
+      }
+      if (took) keep = tmp;
+    }
+    if (!keep.empty()) std::copy(keep.begin(), keep.end(), ids.begin() + lo);
+  } else {
+    double ext = -1;
+    for (int a = 0; a < 3; a++) {
+      double cmn = 1e300, cmx = -1e300;
+      for (int k = lo; k < hi; k++) { const float4 &q = sph[ids[k]]; const double v = a == 0 ? q.x : a == 1 ? q.y : q.z; cmn = std::min(cmn, v); cmx = std::max(cmx, v); }
+      if (cmx - cmn > ext) { ext = cmx - cmn; axis = a; }
+    }
+    std::nth_element(ids.begin() + lo, ids.begin() + mid, ids.begin() + hi, [&](int x, int y) {
+      const float4 &a = sph[x], &b = sph[y];
+      return (axis == 0 ? a.x : axis == 1 ? a.y : a.z) < (axis == 0 ? b.x : axis == 1 ? b.y : b.z);
+    });
   }
-  const int mid = (lo + hi) / 2;
-  std::nth_element(ids.begin() + lo, ids.begin() + mid, ids.begin() + hi, [&](int x, int y) {
-    const float4 &a = sph[x], &b = sph[y];
-    return (axis == 0 ? a.x : axis == 1 ? a.y : a.z) < (axis == 0 ? b.x : axis == 1 ? b.y : b.z);
-  });
   int l = 0, r = 0;
   if (!bvh_build_rec(sph, ids, lo, mid, depth + 1, out, &l)) return false;
   if (!bvh_build_rec(sph, ids, mid, hi, depth + 1, out, &r)) return false;
@@ -442,6 +475,10 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
   lb.items.resize(total + 1);
   size_t base = 0;
   for (size_t g = 0; g < pairs.size(); g++) {
+    // within a cell: largest first (a shadow query stops at its first occluder, and the order is free)
+    std::stable_sort(pairs[g].begin(), pairs[g].end(), [&](const std::pair<int, int> &x, const std::pair<int, int> &y) {
+      return fabsf(sph[x.second].w) > fabsf(sph[y.second].w);
+    });
     std::vector<unsigned> c((size_t)CELLS + 1, 0u);
     for (auto &pr : pairs[g]) c[pr.first + 1]++;
     for (int k = 0; k < CELLS; k++) c[k + 1] += c[k];
@@ -489,6 +526,9 @@ int rt_dbg_qindex_prune(const float *node4, const float *P3, const float *d3, in
   return 0;
 }
 
+static long long g_dbg_nodes = 0;
+long long rt_dbg_qindex_last_nodes(void) { return g_dbg_nodes; }
+
 int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const float *d3, int n_rays, int nearest,
                         const float *best_t, unsigned char *visited) {
   if (!q10 || n_quadrics <= 0 || !visited) return -1;
@@ -496,6 +536,7 @@ int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const
   for (int k = 0; k < n_quadrics; k++) params.push_back(q10 + 10 * (size_t)k);
   QuadricIndex qi;
   build_quadric_index(params, qi);
+  g_dbg_nodes = 0;
   for (int r = 0; r < n_rays; r++) {
     unsigned char *v = visited + (size_t)r * n_quadrics;
     memset(v, 0, n_quadrics);
@@ -504,6 +545,7 @@ int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const
     std::vector<int> stack(1, 0);
     while (!stack.empty()) {
       const int k = stack.back(); stack.pop_back();
+      g_dbg_nodes++;
       const float4 mg = qi.marg[k];
       const QIndexConsts qk = {mg.x, qi.behind_rel, mg.y, mg.z, mg.w};
       if (qnode_prune(qi.bvh.node[k], P3[3 * r], P3[3 * r + 1], P3[3 * r + 2], d3[3 * r], d3[3 * r + 1], d3[3 * r + 2],
