@@ -288,6 +288,18 @@ bool bvh_build_rec(const std::vector<float4> &sph, std::vector<int> &ids, int lo
   return true;
 }
 
+// Children's bounding spheres stored with the parent ({left, right} at 2k, 2k+1), so a traversal step fetches both
+// with one index; `per_node` (optional) is copied the same way.
+void bvh_child_pairs(const SphereBvh &b, const std::vector<float4> &per_node, std::vector<float4> &pair) {
+  pair.assign(2 * b.node.size() + 2, make_float4(0.f, 0.f, 0.f, 0.f));
+  for (size_t k = 0; k < b.node.size(); k++) {
+    const int2 kid = b.kids[k];
+    if (kid.x < 0) continue;
+    pair[2 * k] = per_node[kid.x];
+    pair[2 * k + 1] = per_node[kid.y & 0x0fffffff];
+  }
+}
+
 bool build_sphere_bvh(const std::vector<float4> &sph, int n_sph, SphereBvh &out) {
   std::vector<int> ids(n_sph);
   for (int i = 0; i < n_sph; i++) ids[i] = i;
@@ -775,7 +787,10 @@ int rt_scene_upload(const rt_scene *scene) {
   struct Sec { const void *src; size_t bytes; size_t off; };
   std::vector<float4> lb_hot;
   if (have_lb) { lb_hot.resize(lb.items.size()); for (size_t k = 0; k + 1 < lb.items.size(); k++) lb_hot[k] = sph_hot[lb.items[k]]; }
-  Sec secs[25] = {
+  std::vector<float4> bvh_pair, qbvh_pair, qbvh_mpair;
+  if (have_lb) bvh_child_pairs(bvh, bvh.node, bvh_pair);
+  if (n_qidx) { bvh_child_pairs(qbvh, qbvh.node, qbvh_pair); bvh_child_pairs(qbvh, qbvh_marg, qbvh_mpair); }
+  Sec secs[28] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
@@ -790,7 +805,9 @@ int rt_scene_upload(const rt_scene *scene) {
       {qbvh.node.data(), n_qidx ? qbvh.node.size() * 16 : 0, 0}, {qbvh.kids.data(), n_qidx ? qbvh.kids.size() * 8 : 0, 0},
       {qbvh_marg.data(), n_qidx ? qbvh_marg.size() * 16 : 0, 0},
       {lbq.start.data(), have_lbq ? lbq.start.size() * 4 : 0, 0}, {lbq.items.data(), have_lbq ? lbq.items.size() * 4 : 0, 0},
-      {lbq.caps.data(), have_lbq ? lbq.caps.size() * 4 : 0, 0}};
+      {lbq.caps.data(), have_lbq ? lbq.caps.size() * 4 : 0, 0},
+      {bvh_pair.data(), have_lb ? bvh_pair.size() * 16 : 0, 0}, {qbvh_pair.data(), n_qidx ? qbvh_pair.size() * 16 : 0, 0},
+      {qbvh_mpair.data(), n_qidx ? qbvh_mpair.size() * 16 : 0, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -829,6 +846,9 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.lbq_start = have_lbq ? (const unsigned *)(b + secs[22].off) : nullptr;
     sc.lbq_items = have_lbq ? (const int *)(b + secs[23].off) : nullptr;
     sc.lbq_caps = have_lbq ? (const float *)(b + secs[24].off) : nullptr;
+    sc.bvh_pair = have_lb ? (const float4 *)(b + secs[25].off) : nullptr;
+    sc.qbvh_pair = n_qidx ? (const float4 *)(b + secs[26].off) : nullptr;
+    sc.qbvh_mpair = n_qidx ? (const float4 *)(b + secs[27].off) : nullptr;
     sc.n_qidx = n_qidx;
     sc.q_behind_rel = q_behind_rel;
   }

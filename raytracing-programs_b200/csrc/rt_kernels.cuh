@@ -522,31 +522,46 @@ RT_DEV void refl_test_sphere(const DevScene &sc, const v3 P, const v3 dj, const 
 template <bool ANY>
 RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_sph, float &best_t, int &best_idx,
                       unsigned &n_cand, unsigned &n_tests) {
-  int stack[32];
-  int sp = 0;
-  stack[sp++] = 0;
-  while (sp > 0) {
-    const int k = stack[--sp];
-    const float4 nd = sc.bvh_node[k];
+  // node test: enter?  key: no member can report a t below key / 1.001 (the "beyond" margin taken off already)
+  auto enter = [&](const float4 nd, float &key) -> bool {
     const float wx = P.x - nd.x, wy = P.y - nd.y, wz = P.z - nd.z;
     const float Tn = __fmaf_rn(wz, wz, __fmaf_rn(wy, wy, wx * wx));
     const float en = __fmaf_rn(d.z, wz, __fmaf_rn(d.y, wy, d.x * wx));
     const float reach = sqrtf(Tn) + nd.w;                      // >= sqrt(T) of every member
     const float rinf = __fmaf_rn(nd.w, 1.0001f, 0.0029296875f * reach);  // Rn (1 + 1e-4) + (2^-9 + 2^-10) reach
     // line misses the inflated node?  (Tn - en^2 is the squared distance, float slack 1e-5 Tn)
-    if (!(Tn - en * en <= __fmaf_rn(rinf, rinf, 1e-5f * Tn))) continue;
+    if (!(Tn - en * en <= __fmaf_rn(rinf, rinf, 1e-5f * Tn))) return false;
     const float rbehind = __fmaf_rn(nd.w, 1.001f, 0.015625f * reach);     // Rn (1 + 1e-3) + 2^-6 reach
-    if (en > rbehind) continue;                                // whole node behind the origin
-    if (!ANY && (-en - rinf) > __fmaf_rn(best_t, 1.001f, 4e-3f * reach)) continue;   // whole node beyond the best hit
+    if (en > rbehind) return false;                            // whole node behind the origin
+    key = (-en - rinf) - 4e-3f * reach;
+    return ANY || !(key > best_t * 1.001f);                    // whole node beyond the best hit
+  };
+  int stack[32];
+  float skey[32];
+  int sp = 0, k = 0;
+  float key0;
+  if (!enter(sc.bvh_node[0], key0)) return false;
+  for (;;) {
     const int2 kid = sc.bvh_kids[k];
+    bool descend = false;
     if (kid.x >= 0) {
-      // children were split along axis (kid.y >> 28), left = lower coordinates: enter the nearer one first
-      // (pushed last), so a nearest-hit search finds a small best_t early and prunes the rest
+      // both children's spheres come with the parent: test both, go into the nearer one (children were split
+      // along axis kid.y >> 28, left = lower coordinates), keep the other for later
       const int axis = kid.y >> 28, right = kid.y & 0x0fffffff;
+      const float4 nl = sc.bvh_pair[2 * k], nr = sc.bvh_pair[2 * k + 1];
+      float kl = 0.f, kr = 0.f;
+      const bool hl = enter(nl, kl), hr = enter(nr, kr);
       const float da = axis == 0 ? d.x : axis == 1 ? d.y : d.z;
       const bool left_first = da >= 0.0f;
-      stack[sp++] = left_first ? right : kid.x;                // depth <= 28 (host), one net entry per level
-      stack[sp++] = left_first ? kid.x : right;
+      if (hl && hr) {
+        stack[sp] = left_first ? right : kid.x;                // depth <= 28 (host), one net entry per level
+        skey[sp++] = left_first ? kr : kl;
+        k = left_first ? kid.x : right;
+        descend = true;
+      } else if (hl || hr) {
+        k = hl ? kid.x : right;
+        descend = true;
+      }
     } else {
       const int first = -kid.x - 1;
       for (int i = 0; i < kid.y; i++) {
@@ -557,14 +572,16 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_
         else refl_test_sphere(sc, P, d, ss, best_t, best_idx, n_cand);
       }
     }
+    if (descend) continue;
+    bool got = false;
+    while (sp > 0) {
+      --sp;
+      if (ANY || !(skey[sp] > best_t * 1.001f)) { k = stack[sp]; got = true; break; }   // best_t may have come down since the push
+    }
+    if (!got) return false;
   }
-  return false;
 }
 
-// Traversal of the hierarchy over the indexed ellipsoids (quadric slots 0 .. n_qidx-1, rt_qindex.cuh) for one
-// ray; what a leaf lets through takes the same chain as resolve_quadrics: reject filter, then the reference's
-// expression tree.  ZRULE: the hit-point rule of C/raycast.c:492-494
-// (every ray but the primary ones).  ANY = true: shadow query, returns at the first hit.
 // One ray against quadric slot kk, the chain of resolve_quadrics: reject filter, then the reference's expression
 // tree and (ZRULE) the hit-point rule of C/raycast.c:492-494.  Returns whether the reference reports a t; the
 // caller applies its own acceptance (0 < t < inf for a shadow ray, better_hit for a nearest-hit search).
@@ -583,21 +600,35 @@ RT_DEV bool quadric_reported(const DevScene &sc, const v3 P, const v3 d, const i
 template <bool ANY, bool ZRULE>
 __device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj, float &best_t, int &best_idx,
                                         unsigned &n_cand, unsigned &n_tests) {
-  int stack[32];
-  int sp = 0;
-  stack[sp++] = 0;
-  while (sp > 0) {
-    const int k = stack[--sp];
-    const float4 mg = sc.qbvh_marg[k];
+  auto enter = [&](const float4 nd, const float4 mg, float &key) -> bool {
     const QIndexConsts qk = {mg.x, sc.q_behind_rel, mg.y, mg.z, mg.w};
-    if (qnode_prune(sc.qbvh_node[k], P.x, P.y, P.z, d.x, d.y, d.z, !ANY, best_t, qk)) continue;
+    return qnode_prune(nd, P.x, P.y, P.z, d.x, d.y, d.z, !ANY, best_t, qk, &key) == 0;
+  };
+  int stack[32];
+  float skey[32];
+  int sp = 0, k = 0;
+  float key0;
+  if (!enter(sc.qbvh_node[0], sc.qbvh_marg[0], key0)) return false;
+  for (;;) {
     const int2 kid = sc.qbvh_kids[k];
+    bool descend = false;
     if (kid.x >= 0) {
       const int axis = kid.y >> 28, right = kid.y & 0x0fffffff;
+      const float4 nl = sc.qbvh_pair[2 * k], nr = sc.qbvh_pair[2 * k + 1];
+      const float4 ml = sc.qbvh_mpair[2 * k], mr = sc.qbvh_mpair[2 * k + 1];
+      float kl = 0.f, kr = 0.f;
+      const bool hl = enter(nl, ml, kl), hr = enter(nr, mr, kr);
       const float da = axis == 0 ? d.x : axis == 1 ? d.y : d.z;
       const bool left_first = da >= 0.0f;
-      stack[sp++] = left_first ? right : kid.x;                // depth <= 28 (host), one net entry per level
-      stack[sp++] = left_first ? kid.x : right;
+      if (hl && hr) {
+        stack[sp] = left_first ? right : kid.x;                // depth <= 28 (host), one net entry per level
+        skey[sp++] = left_first ? kr : kl;
+        k = left_first ? kid.x : right;
+        descend = true;
+      } else if (hl || hr) {
+        k = hl ? kid.x : right;
+        descend = true;
+      }
     } else {
       const int first = -kid.x - 1;
       for (int i = 0; i < kid.y; i++) {
@@ -611,8 +642,14 @@ __device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3
         else if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
       }
     }
+    if (descend) continue;
+    bool got = false;
+    while (sp > 0) {
+      --sp;
+      if (ANY || !(skey[sp] > best_t * 1.001f)) { k = stack[sp]; got = true; break; }
+    }
+    if (!got) return false;
   }
-  return false;
 }
 
 // Scan variants: the bundle scans are compiled for NR, NR-2, NR-4, ... >= 3 ray slots; a warp runs

@@ -38,12 +38,14 @@ struct QIndexConsts {   // maxima over the ellipsoids of a node
 };
 
 // Node (or item) test for the ray P + t d.  0 = enter, 1 = the line misses, 2 = wholly behind the origin,
-// 3 = (nearest-hit search only) wholly beyond best_t.  nd = {centre, radius}.
+// 3 = (nearest-hit search only) wholly beyond best_t.  nd = {centre, radius}.  *key (when the node is entered or
+// beyond): the node holds no t below key / 1.001, so a traversal may drop it later once best_t * 1.001 < key.
 __host__ __device__ inline int qnode_prune(const float4 nd, const float px, const float py, const float pz, const float dx,
                                            const float dy, const float dz, const bool nearest, const float best_t,
-                                           const QIndexConsts k) {
+                                           const QIndexConsts k, float *key = nullptr) {
   const float wx = px - nd.x, wy = py - nd.y, wz = pz - nd.z;
   const float Tn = fmaf(wz, wz, fmaf(wy, wy, wx * wx));
+  if (key) *key = -3.0e38f;
   if (!(Tn < 1e30f)) return 0;                                           // overflow or NaN origin: no pruning
   const float en = fmaf(dz, wz, fmaf(dy, wy, dx * wx));
   const float reach = sqrtf(Tn) + nd.w;                                  // >= |P - c| + r of every member
@@ -51,7 +53,9 @@ __host__ __device__ inline int qnode_prune(const float4 nd, const float px, cons
   if (!(Tn - en * en <= fmaf(rinf, rinf, 1e-5f * Tn))) return 1;        // 1e-5 Tn: float slack of this line, |d| != 1
   const float rbehind = fmaf(nd.w, 1.001f, k.behind_rel * reach) + k.behind_abs;
   if (en > rbehind) return 2;
-  if (nearest && (-en - rinf) > fmaf(best_t, 1.001f, k.t_rel * reach) + k.t_abs) return 3;
+  const float kk = (-en - rinf) - (k.t_rel * reach + k.t_abs);
+  if (key) *key = kk;
+  if (nearest && kk > best_t * 1.001f) return 3;
   return 0;
 }
 

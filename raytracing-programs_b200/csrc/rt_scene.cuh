@@ -39,12 +39,14 @@ struct DevScene {
   // (in this mode the host lays the spheres out in leaf order).
   const float4 *bvh_node;
   const int2 *bvh_kids;
+  const float4 *bvh_pair;   // [2k], [2k+1]: bvh_node of the left and right child of inner node k (one fetch per traversal step)
   // The same kind of hierarchy over the ellipsoids among the quadrics (rt_qindex.cuh): they take quadric slots
   // 0 .. n_qidx-1 in leaf order, every other quadric follows and is scanned as before.  qbvh_node = NULL or
   // n_qidx = 0: no quadric index.
   const float4 *qbvh_node;
   const int2 *qbvh_kids;
   const float4 *qbvh_marg;  // per node {miss_rel, behind_abs, t_rel, t_abs}: the largest margins its members need
+  const float4 *qbvh_pair, *qbvh_mpair;   // children's node and margin entries stored with the parent, as bvh_pair
   int n_qidx;
   float q_behind_rel;
   // Light buffer over the indexed ellipsoids (same layout as lb_*; items are quadric slots); NULL: shadow rays walk
