@@ -365,8 +365,12 @@ void build_quadric_index(const std::vector<const float *> &params, QuadricIndex 
 // indexed ellipsoids (rt_qindex.cuh): the reference can only report ellipsoid s if the line enters {q <= delta(|P - c|)},
 // which lies within sqrt((K + a0 + a1 s + a2 s^2)/lmin) of the centre, s = |P - c| <= Dcap + |c - L|; only the four
 // nearest distance levels are built for them (farther out the inflated ellipsoids fill too many cells: hierarchy).
+// scene = NULL: the same cube map for the primary rays -- one pseudo light at the camera (0,0,0), one level with
+// Dcap = 0 (a primary ray starts AT the apex, so T = |C|^2 exactly): level 0 of "light" 0 lists what a ray leaving
+// the origin in that cell's directions can be reported to hit.
 bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, int n_sph, const std::vector<QLbItem> *qit, LightBuffer &lb) {
-  const int R = RT_LB_RES, CELLS = 6 * R * R, nl = scene->num_lights;
+  const bool camera = scene == nullptr;
+  const int R = RT_LB_RES, CELLS = 6 * R * R, nl = camera ? 1 : scene->num_lights;
   std::vector<double> cb(3 * (size_t)CELLS), cbeta(CELLS), ccos(CELLS), csin(CELLS);
   for (int face = 0; face < 6; face++)
     for (int j = 0; j < R; j++)
@@ -408,8 +412,8 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
   std::vector<std::vector<unsigned>> cnt((size_t)nl * RT_LB_LEVELS);           // per (light, level): CSR counts
   std::vector<std::vector<std::pair<int, int>>> pairs((size_t)nl * RT_LB_LEVELS);   // (cell, sphere)
   auto work = [&](int l) {
-    const rt_light &t = scene->lights[l];
-    const double L[3] = {t.position[0], t.position[1], t.position[2]};
+    double L[3] = {0.0, 0.0, 0.0};
+    if (!camera) { const rt_light &t = scene->lights[l]; L[0] = t.position[0]; L[1] = t.position[1]; L[2] = t.position[2]; }
     if (!std::isfinite(L[0]) || !std::isfinite(L[1]) || !std::isfinite(L[2])) return;
     double Rl = 0;
     for (int s = 0; s < n_sph; s++) {
@@ -421,9 +425,9 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
     const double mult[RT_LB_LEVELS] = {0.35, 0.7, 1.4, 2.8, 8.0, 32.0};
     float capf[RT_LB_LEVELS];
     for (int lv = 0; lv < RT_LB_LEVELS; lv++) {
-      const double Dcap = Rl * mult[lv];
+      const double Dcap = camera ? 0.0 : Rl * mult[lv];
       capf[lv] = (float)((Dcap * (1.0 - 1e-3)) * (Dcap * (1.0 - 1e-3)));
-      if (qit && lv >= 4) { capf[lv] = -1.f; continue; }
+      if ((qit && lv >= 4) || (camera && lv >= 1)) { capf[lv] = -1.f; continue; }
       auto &pv = pairs[(size_t)l * RT_LB_LEVELS + lv];
       for (int s = 0; s < n_sph; s++) {
         const double dx = sph[s].x - L[0], dy = sph[s].y - L[1], dz = sph[s].z - L[2], r = fabs((double)sph[s].w);
@@ -760,6 +764,9 @@ int rt_scene_upload(const rt_scene *scene) {
     quad_order.swap(reordered);
   }
   const int n_qidx = qi.n_idx;
+  LightBuffer cam, camq;                  // the cube map of the primary rays (apex = the camera), spheres and ellipsoids
+  const bool have_cam = have_lb && !getenv("RT_NO_CAMGRID") && build_light_buffer(nullptr, sph, n_sph_real, nullptr, cam);
+  const bool have_camq = have_cam && qi.n_idx > 0 && build_light_buffer(nullptr, qi.slot_ball, qi.n_idx, &qi.slot_q, camq);
   LightBuffer lbq;                        // the same cube maps over the indexed ellipsoids
   const bool have_lbq = n_qidx > 0 && !getenv("RT_NO_QLB") && build_light_buffer(scene, qi.slot_ball, n_qidx, &qi.slot_q, lbq);
   const SphereBvh &qbvh = qi.bvh;
@@ -790,7 +797,7 @@ int rt_scene_upload(const rt_scene *scene) {
   std::vector<float4> bvh_pair, qbvh_pair, qbvh_mpair;
   if (have_lb) bvh_child_pairs(bvh, bvh.node, bvh_pair);
   if (n_qidx) { bvh_child_pairs(qbvh, qbvh.node, qbvh_pair); bvh_child_pairs(qbvh, qbvh_marg, qbvh_mpair); }
-  Sec secs[28] = {
+  Sec secs[32] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
@@ -807,7 +814,9 @@ int rt_scene_upload(const rt_scene *scene) {
       {lbq.start.data(), have_lbq ? lbq.start.size() * 4 : 0, 0}, {lbq.items.data(), have_lbq ? lbq.items.size() * 4 : 0, 0},
       {lbq.caps.data(), have_lbq ? lbq.caps.size() * 4 : 0, 0},
       {bvh_pair.data(), have_lb ? bvh_pair.size() * 16 : 0, 0}, {qbvh_pair.data(), n_qidx ? qbvh_pair.size() * 16 : 0, 0},
-      {qbvh_mpair.data(), n_qidx ? qbvh_mpair.size() * 16 : 0, 0}};
+      {qbvh_mpair.data(), n_qidx ? qbvh_mpair.size() * 16 : 0, 0},
+      {cam.start.data(), have_cam ? cam.start.size() * 4 : 0, 0}, {cam.items.data(), have_cam ? cam.items.size() * 4 : 0, 0},
+      {camq.start.data(), have_camq ? camq.start.size() * 4 : 0, 0}, {camq.items.data(), have_camq ? camq.items.size() * 4 : 0, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -849,13 +858,18 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.bvh_pair = have_lb ? (const float4 *)(b + secs[25].off) : nullptr;
     sc.qbvh_pair = n_qidx ? (const float4 *)(b + secs[26].off) : nullptr;
     sc.qbvh_mpair = n_qidx ? (const float4 *)(b + secs[27].off) : nullptr;
+    sc.cam_start = have_cam ? (const unsigned *)(b + secs[28].off) : nullptr;
+    sc.cam_items = have_cam ? (const int *)(b + secs[29].off) : nullptr;
+    sc.camq_start = have_camq ? (const unsigned *)(b + secs[30].off) : nullptr;
+    sc.camq_items = have_camq ? (const int *)(b + secs[31].off) : nullptr;
     sc.n_qidx = n_qidx;
     sc.q_behind_rel = q_behind_rel;
   }
   if (getenv("RT_VERBOSE"))
-    fprintf(stderr, "rt_scene_upload: %d spheres, %d planes, %d quadrics (%d indexed), light buffer %s (%zu items), ellipsoid light buffer %s (%zu items), blob %zu bytes\n",
+    fprintf(stderr, "rt_scene_upload: %d spheres, %d planes, %d quadrics (%d indexed), light buffer %s (%zu items), ellipsoid light buffer %s (%zu items), camera grid %zu + %zu items, blob %zu bytes\n",
             n_sph_real, (int)pln_idx.size(), (int)quad_idx.size(), n_qidx, have_lb ? "yes" : "no", have_lb ? lb.items.size() : (size_t)0,
-            have_lbq ? "yes" : "no", have_lbq ? lbq.items.size() : (size_t)0, total);
+            have_lbq ? "yes" : "no", have_lbq ? lbq.items.size() : (size_t)0, have_cam ? cam.items.size() : (size_t)0,
+            have_camq ? camq.items.size() : (size_t)0, total);
   g_have_scene = true;
   g_n_lights = nl;
   g_n_shapes = n;

@@ -126,6 +126,10 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_
 template <bool ANY, bool ZRULE>
 __device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj, float &best_t, int &best_idx,
                                         unsigned &n_cand, unsigned &n_tests);
+template <bool ZRULE>
+RT_DEV bool quadric_reported(const DevScene &sc, const v3 P, const v3 d, const int kk, float &t, unsigned &n_cand);
+RT_DEV void refl_test_sphere(const DevScene &sc, const v3 P, const v3 dj, const int ss, float &best_t, int &best_idx,
+                             unsigned &n_cand);
 #define RT_PRIM_PX_BRUTE 4   // pixels (= primary rays) per thread: one sphere load feeds four reject tests
 template <bool ACCEL>
 __global__ void __launch_bounds__(256)
@@ -167,7 +171,14 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
       for (int k = 0; k < RT_PRIM_PX; k++) {
         if (!((live >> k) & 1u)) continue;
         unsigned nt = 0, nc = 0;
-        bvh_trace<false>(sc, o, d[k], -1, best_t[k], best_idx[k], nc, nt);
+        const int cell = sc.cam_start != nullptr ? lb_cell(d[k].x, d[k].y, d[k].z) : -1;
+        if (cell >= 0) {
+          // every primary ray leaves (0,0,0): the camera's own cube map lists what its cell can reach
+          const unsigned k1 = sc.cam_start[cell + 1];
+          for (unsigned q = sc.cam_start[cell]; q < k1; q++) { nt++; refl_test_sphere(sc, o, d[k], sc.cam_items[q], best_t[k], best_idx[k], nc); }
+        } else {
+          bvh_trace<false>(sc, o, d[k], -1, best_t[k], best_idx[k], nc, nt);
+        }
         n_cand += nc; n_sph += nt;
       }
     } else {
@@ -227,7 +238,18 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
         for (int k = 0; k < RT_PRIM_PX; k++) {
           if (!((live >> k) & 1u)) continue;
           unsigned nt = 0, nc = 0;
-          qbvh_trace<false, false>(sc, o, d[k], -1, best_t[k], best_idx[k], nc, nt);
+          const int cell = sc.camq_start != nullptr ? lb_cell(d[k].x, d[k].y, d[k].z) : -1;
+          if (cell >= 0) {
+            const unsigned k1 = sc.camq_start[cell + 1];
+            for (unsigned q = sc.camq_start[cell]; q < k1; q++) {
+              const int kk = sc.camq_items[q];
+              float t;
+              nt++;
+              if (quadric_reported<false>(sc, o, d[k], kk, t, nc) && better_hit(t, sc.quad_idx[kk], best_t[k], best_idx[k])) { best_t[k] = t; best_idx[k] = sc.quad_idx[kk]; }
+            }
+          } else {
+            qbvh_trace<false, false>(sc, o, d[k], -1, best_t[k], best_idx[k], nc, nt);
+          }
           n_cand += nc; n_quad += nt;
         }
       }

@@ -54,6 +54,11 @@ struct DevScene {
   const unsigned *lbq_start;
   const int *lbq_items;
   const float *lbq_caps;
+  // The same cube map with the camera (0,0,0) as apex, for the primary rays: level 0 of "light" 0 (lb_* layout).
+  const unsigned *cam_start;   // spheres; NULL: primary rays walk the hierarchies
+  const int *cam_items;
+  const unsigned *camq_start;  // indexed ellipsoids; NULL: hierarchy
+  const int *camq_items;
 };
 #define RT_LB_RES 32
 #define RT_LB_LEVELS 6
