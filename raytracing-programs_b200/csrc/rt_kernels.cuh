@@ -563,10 +563,18 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_
   int sp = 0, k = 0;
   float key0;
   if (!enter(sc.bvh_node[0], key0)) return false;
+  auto pop = [&]() -> bool {
+    while (sp > 0) {
+      --sp;
+      if (ANY || !(skey[sp] > best_t * 1.001f)) { k = stack[sp]; return true; }   // best_t may have come down since the push
+    }
+    return false;
+  };
+  // "while-while": walk inner nodes until a leaf turns up, then test the leaf -- the lanes of a warp spend their
+  // time in the same one of the two loops
   for (;;) {
-    const int2 kid = sc.bvh_kids[k];
-    bool descend = false;
-    if (kid.x >= 0) {
+    int2 kid = sc.bvh_kids[k];
+    while (kid.x >= 0) {
       // both children's spheres come with the parent: test both, go into the nearer one (children were split
       // along axis kid.y >> 28, left = lower coordinates), keep the other for later
       const int axis = kid.y >> 28, right = kid.y & 0x0fffffff;
@@ -579,28 +587,22 @@ RT_DEV bool bvh_trace(const DevScene &sc, const v3 P, const v3 d, const int obj_
         stack[sp] = left_first ? right : kid.x;                // depth <= 28 (host), one net entry per level
         skey[sp++] = left_first ? kr : kl;
         k = left_first ? kid.x : right;
-        descend = true;
       } else if (hl || hr) {
         k = hl ? kid.x : right;
-        descend = true;
+      } else if (!pop()) {
+        return false;
       }
-    } else {
-      const int first = -kid.x - 1;
-      for (int i = 0; i < kid.y; i++) {
-        const int ss = first + i;                              // leaves are runs of consecutive sphere slots
-        n_tests++;
-        if (ss == obj_sph) continue;                           // C/raycast.c:450
-        if (ANY) { if (shadow_hits_sphere(sc, P, d, ss, sc.sph_hot[ss], n_cand)) return true; }
-        else refl_test_sphere(sc, P, d, ss, best_t, best_idx, n_cand);
-      }
+      kid = sc.bvh_kids[k];
     }
-    if (descend) continue;
-    bool got = false;
-    while (sp > 0) {
-      --sp;
-      if (ANY || !(skey[sp] > best_t * 1.001f)) { k = stack[sp]; got = true; break; }   // best_t may have come down since the push
+    const int first = -kid.x - 1;
+    for (int i = 0; i < kid.y; i++) {
+      const int ss = first + i;                                // leaves are runs of consecutive sphere slots
+      n_tests++;
+      if (ss == obj_sph) continue;                             // C/raycast.c:450
+      if (ANY) { if (shadow_hits_sphere(sc, P, d, ss, sc.sph_hot[ss], n_cand)) return true; }
+      else refl_test_sphere(sc, P, d, ss, best_t, best_idx, n_cand);
     }
-    if (!got) return false;
+    if (!pop()) return false;
   }
 }
 
@@ -631,10 +633,16 @@ __device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3
   int sp = 0, k = 0;
   float key0;
   if (!enter(sc.qbvh_node[0], sc.qbvh_marg[0], key0)) return false;
+  auto pop = [&]() -> bool {
+    while (sp > 0) {
+      --sp;
+      if (ANY || !(skey[sp] > best_t * 1.001f)) { k = stack[sp]; return true; }
+    }
+    return false;
+  };
   for (;;) {
-    const int2 kid = sc.qbvh_kids[k];
-    bool descend = false;
-    if (kid.x >= 0) {
+    int2 kid = sc.qbvh_kids[k];
+    while (kid.x >= 0) {
       const int axis = kid.y >> 28, right = kid.y & 0x0fffffff;
       const float4 nl = sc.qbvh_pair[2 * k], nr = sc.qbvh_pair[2 * k + 1];
       const float4 ml = sc.qbvh_mpair[2 * k], mr = sc.qbvh_mpair[2 * k + 1];
@@ -646,31 +654,25 @@ __device__ __noinline__ bool qbvh_trace(const DevScene &sc, const v3 P, const v3
         stack[sp] = left_first ? right : kid.x;                // depth <= 28 (host), one net entry per level
         skey[sp++] = left_first ? kr : kl;
         k = left_first ? kid.x : right;
-        descend = true;
       } else if (hl || hr) {
         k = hl ? kid.x : right;
-        descend = true;
+      } else if (!pop()) {
+        return false;
       }
-    } else {
-      const int first = -kid.x - 1;
-      for (int i = 0; i < kid.y; i++) {
-        const int kk = first + i;                              // leaves are runs of consecutive quadric slots
-        n_tests++;
-        const int idx = sc.quad_idx[kk];
-        if (idx == obj) continue;                              // C/raycast.c:450
-        float t;
-        if (!quadric_reported<ZRULE>(sc, P, d, kk, t, n_cand)) continue;
-        if (ANY) { if (t > 0.0f && t < RT_INF) return true; }
-        else if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
-      }
+      kid = sc.qbvh_kids[k];
     }
-    if (descend) continue;
-    bool got = false;
-    while (sp > 0) {
-      --sp;
-      if (ANY || !(skey[sp] > best_t * 1.001f)) { k = stack[sp]; got = true; break; }
+    const int first = -kid.x - 1;
+    for (int i = 0; i < kid.y; i++) {
+      const int kk = first + i;                                // leaves are runs of consecutive quadric slots
+      n_tests++;
+      const int idx = sc.quad_idx[kk];
+      if (idx == obj) continue;                                // C/raycast.c:450
+      float t;
+      if (!quadric_reported<ZRULE>(sc, P, d, kk, t, n_cand)) continue;
+      if (ANY) { if (t > 0.0f && t < RT_INF) return true; }
+      else if (better_hit(t, idx, best_t, best_idx)) { best_t = t; best_idx = idx; }
     }
-    if (!got) return false;
+    if (!pop()) return false;
   }
 }
 
