@@ -127,6 +127,40 @@ def test_accel_quadric_index(renderer, tmp_path):
 
 
 @pytest.mark.timeout(900)
+@pytest.mark.parametrize("shell", ["ellipsoid", "sphere"])
+def test_accel_camera_inside_objects(renderer, tmp_path, shell):
+    """The primary rays' cube map with the camera inside an ellipsoid / a sphere (every cell must list it; the shell's
+    inside is lit because a surface skips itself, everything else is in its shadow: the reference's shadow rays have
+    no t_max), objects behind the camera (mirrors show them), one on the optical axis."""
+    rng = np.random.default_rng(4)
+    lines = ["camera, width: 2.4, height: 1.6",
+             "sphere, radius: 40, position: [1, 2, -5], diffuse_color: [0.5, 0.6, 0.9], specular_color: [1, 1, 1], reflectivity: 0.2, refractivity: 0, ior: 1"
+             if shell == "sphere" else _ellipsoid_line(rng, np.array([0.5, -0.5, -2.0]), [25.0, 18.0, 30.0], True, 0.3),
+             "sphere, radius: 1, position: [0, 0, -6], diffuse_color: [1, 0.1, 0.1], specular_color: [1, 1, 1], reflectivity: 0.8, refractivity: 0, ior: 1",
+             "sphere, radius: 1.5, position: [4, 4, -4], diffuse_color: [0.1, 1, 0.1], specular_color: [1, 1, 1], reflectivity: 0.5, refractivity: 0, ior: 1",
+             "sphere, radius: 2, position: [0, 1, 7], diffuse_color: [1, 1, 0.1], specular_color: [1, 1, 1], reflectivity: 0, refractivity: 0, ior: 1",
+             "plane, normal: [0, 1, 0], position: [0, -3, 0], diffuse_color: [0.6, 0.6, 0.6], specular_color: [1, 1, 1], reflectivity: 0.5"]
+    for k in range(14):
+        c = np.array([rng.uniform(-8, 8), rng.uniform(-2, 6), rng.uniform(-12, 9)])
+        if np.linalg.norm(c) < 2.5:
+            c *= 3.0
+        lines.append(_ellipsoid_line(rng, c, rng.uniform(0.4, 1.4, 3), k % 2 == 0, [0, 0.5, 0.9][k % 3]))
+    lines += ["light, color: [2, 2, 2], position: [3, 6, -2], radial-a0: 1, radial-a1: 0, radial-a2: 0.003",
+              "light, color: [2, 1, 1], position: [-5, 4, 3], radial-a0: 1, radial-a1: 0, radial-a2: 0.003"]
+    p = tmp_path / "inside.scene"
+    p.write_text("\n".join(lines) + "\n")
+    for W, H in ((384, 256), (101, 67)):
+        a, sa = render(renderer, str(p), W, H, 0)
+        b, sb = render(renderer, str(p), W, H, 1)
+        assert np.array_equal(a, b), rtlib.compare(a, b)
+        assert (sa.rays, sa.rays_reflection, sa.hit_points) == (sb.rays, sb.rays_reflection, sb.hit_points)   # same hit points found
+        assert sa.rays_reflection > W * H // 4
+        assert np.array_equal(b, rtlib.oracle_render(str(p), W, H))
+    # a sphere keeps its outward normal when hit from inside (C/raycast.c:465-469; only quadrics flip, :521-523): black frame
+    assert shell == "sphere" or (a.max() > 0 and len(np.unique(a)) > 30)
+
+
+@pytest.mark.timeout(900)
 def test_accel_quadric_index_deep_bounces(renderer):
     """C5 with the bounce limit of the reference's CUDA variant (50): long reflection chains between ellipsoids,
     spheres and the tilted floors, accelerated frame = brute-force frame."""
