@@ -215,8 +215,8 @@ def accel_leg(r, sc, W, H, frame, rays, flush):
             ms.append(st.ms_kernels)
     same = bool(torch.equal(frame, frame2))
     m = statistics.median(ms)
-    leg = {"mode": "spheres: light buffer (shadow rays) + bounding-sphere hierarchy; ellipsoids among the quadrics: bounding-sphere "
-                   "hierarchy with certified margins; planes and other quadrics brute force",
+    leg = {"mode": "cube-map lists per light (shadow rays) and for the camera (primary rays) + bounding-sphere hierarchies (reflection "
+                   "rays, far hit points), over the spheres and the ellipsoids among the quadrics; planes and other quadrics brute force",
            "value": rays / m / 1e3, "unit": "Mrays/s", "ms_per_step": m, "mpixels_per_s": W * H / m / 1e3,
            "upload_with_build_ms": build_ms, "frame_equals_brute_force": same,
            "sphere_tests_per_ray": (st.sphere_tests_d) / max(st.rays, 1), "quadric_tests_per_ray": (st.quadric_tests_d) / max(st.rays, 1), "kernel_ms": {"primary": st.ms_primary, "shade": st.ms_shade, "finalize": st.ms_finalize}}
