@@ -691,6 +691,12 @@ int rt_scene_upload(const rt_scene *scene) {
   const bool want_accel = env_accel ? atoi(env_accel) != 0 : g_accel != 0;
   SphereBvh bvh;
   bool have_bvh = false;
+  if (want_accel && sphere_order.empty() && !quad_order.empty()) {
+    // no spheres, but quadrics the index may hold: an empty hierarchy (one leaf without members) keeps the mode on
+    bvh.node.push_back(make_float4(0.f, 0.f, 0.f, 0.f));
+    bvh.kids.push_back(make_int2(-1, 0));
+    have_bvh = true;
+  }
   if (want_accel && !sphere_order.empty()) {
     std::vector<float4> tmp;
     for (int i : sphere_order) { const rt_shape &s = scene->shapes[i]; tmp.push_back(make_float4(s.position[0], s.position[1], s.position[2], s.params[0])); }
@@ -751,7 +757,7 @@ int rt_scene_upload(const rt_scene *scene) {
   const int n_sph_real = (int)slot_count_spheres;
   // light buffer (opt-in: rt_set_accel(1) or RT_ACCEL=1)
   LightBuffer lb;
-  const bool have_lb = have_bvh && nl > 0 && n_sph_real > 0 && build_light_buffer(scene, sph, n_sph_real, nullptr, lb);
+  const bool have_lb = have_bvh && nl > 0 && build_light_buffer(scene, sph, n_sph_real, nullptr, lb);
   // Quadrics: file order; in accel mode the ellipsoids the index can certify (rt_qindex.cuh) come first, in
   // the leaf order of their own bounding-sphere hierarchy.  Any order is parity-safe, as for the spheres.
   QuadricIndex qi;
@@ -765,8 +771,11 @@ int rt_scene_upload(const rt_scene *scene) {
   }
   const int n_qidx = qi.n_idx;
   LightBuffer cam, camq;                  // the cube map of the primary rays (apex = the camera), spheres and ellipsoids
-  const bool have_cam = have_lb && !getenv("RT_NO_CAMGRID") && build_light_buffer(nullptr, sph, n_sph_real, nullptr, cam);
-  const bool have_camq = have_cam && qi.n_idx > 0 && build_light_buffer(nullptr, qi.slot_ball, qi.n_idx, &qi.slot_q, camq);
+  // (usable only if its one level was really built: a scene of absurd extent leaves caps[0] at -1 and no lists)
+  const bool have_cam = have_lb && n_sph_real > 0 && !getenv("RT_NO_CAMGRID") && build_light_buffer(nullptr, sph, n_sph_real, nullptr, cam) &&
+                        cam.caps[0] >= 0.f;
+  const bool have_camq = have_lb && qi.n_idx > 0 && !getenv("RT_NO_CAMGRID") && build_light_buffer(nullptr, qi.slot_ball, qi.n_idx, &qi.slot_q, camq) &&
+                         camq.caps[0] >= 0.f;
   LightBuffer lbq;                        // the same cube maps over the indexed ellipsoids
   const bool have_lbq = n_qidx > 0 && !getenv("RT_NO_QLB") && build_light_buffer(scene, qi.slot_ball, n_qidx, &qi.slot_q, lbq);
   const SphereBvh &qbvh = qi.bvh;

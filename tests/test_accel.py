@@ -161,6 +161,33 @@ def test_accel_camera_inside_objects(renderer, tmp_path, shell):
 
 
 @pytest.mark.timeout(900)
+def test_accel_scene_without_spheres(renderer, tmp_path):
+    """Only quadrics and a plane: the mode stays on with an empty sphere hierarchy, and a scene whose extent is absurd
+    (one ellipsoid 1e17 away) renders through the hierarchies instead of the cube maps."""
+    for far in (False, True):
+        rng = np.random.default_rng(8)
+        lines = ["camera, width: 2, height: 1.5",
+                 "plane, normal: [0, 1, 0], position: [0, -4, 0], diffuse_color: [0.7, 0.7, 0.7], specular_color: [1, 1, 1], reflectivity: 0.3"]
+        for k in range(40):
+            c = np.array([rng.uniform(-10, 10), rng.uniform(-3, 6), -rng.uniform(6, 40)])
+            lines.append(_ellipsoid_line(rng, c, rng.uniform(0.4, 1.8, 3), k % 2 == 1, [0, 0.4, 0.8][k % 3]))
+        if far:
+            lines.append("quadric, diffuse_color: [1, 1, 1], specular_color: [1, 1, 1], a: 1, b: 1, c: 1, d: 0, e: 0, f: 0, "
+                         "g: -2e17, h: 0, i: 0, j: 1e34, reflectivity: 0")
+        lines += ["light, color: [2, 2, 2], position: [5, 12, 0], radial-a0: 1, radial-a1: 0, radial-a2: 0.001",
+                  "light, color: [1, 1, 2], position: [-8, 3, -20], radial-a0: 1, radial-a1: 0, radial-a2: 0.001"]
+        p = tmp_path / f"nospheres{int(far)}.scene"
+        p.write_text("\n".join(lines) + "\n")
+        a, sa = render(renderer, str(p), 320, 240, 0)
+        b, sb = render(renderer, str(p), 320, 240, 1)
+        assert np.array_equal(a, b), rtlib.compare(a, b)
+        assert sa.rays == sb.rays
+        assert sb.quadric_tests_d * 2 < sa.quadric_tests_d, (far, sb.quadric_tests_d, sa.quadric_tests_d)   # the mode is on
+        assert np.array_equal(b, rtlib.oracle_render(str(p), 320, 240))
+        assert a.max() > 0
+
+
+@pytest.mark.timeout(900)
 def test_accel_quadric_index_deep_bounces(renderer):
     """C5 with the bounce limit of the reference's CUDA variant (50): long reflection chains between ellipsoids,
     spheres and the tilted floors, accelerated frame = brute-force frame."""
