@@ -237,11 +237,13 @@ bool bvh_build_rec(const std::vector<float4> &sph, std::vector<int> &ids, int lo
   }
   // Split: sweep the members sorted by centre along each axis and take the cut that minimises
   // n_left * d_left^2 + n_right * d_right^2, d = diagonal of the side's bounding box (a node sphere is built around
-  // that box, and the chance that a ray meets it grows with its cross-section).  Deep down a lopsided tree falls back
-  // to the median along the widest axis, so the depth stays bounded.
+  // that box, and the chance that a ray meets it grows with its cross-section).  Where a lopsided tree comes close to
+  // the depth limit it falls back to the median along the widest axis (balanced from there on).
   int axis = 0, mid = (lo + hi) / 2;
   const int n = hi - lo;
-  if (depth < 14 && !getenv("RT_BVH_MEDIAN")) {
+  int lg = 0;
+  while ((1 << lg) < n) lg++;
+  if (depth + lg + 2 < 28 && !getenv("RT_BVH_MEDIAN")) {     // a median-split subtree of n members is lg levels deep
     double best = 1e300;
     std::vector<int> tmp(ids.begin() + lo, ids.begin() + hi), keep;
     std::vector<double> suf((size_t)n + 1);

@@ -339,3 +339,34 @@ def test_hierarchy_visits_every_reported_quadric(scene, n_rays):
     winners = ts[has] == bn[:, None]
     assert not (winners & (vis2 == 0)).any()
     assert vis2.sum() <= visited[has].sum()
+
+
+@pytest.mark.timeout(600)
+def test_lopsided_hierarchy_stays_within_depth_and_exact():
+    """Ellipsoids in a geometric progression (each as large as all the smaller ones together): the sweep split peels
+    them off one at a time, the builder has to switch to median splits before the traversal stack (32 entries) could
+    overflow, and the index still visits everything the reference reports."""
+    lib, o = _lib()
+    lib.rt_dbg_qindex_visit.argtypes = [FP, C.c_int, FP, FP, C.c_int, C.c_int, FP, C.POINTER(C.c_ubyte)]
+    qs = []
+    for k in range(70):
+        x, r = 1.12 ** k, 0.2 * 1.12 ** k
+        s = 1.0 / (r * r)
+        qs.append([s, s, s * 1.3, 0, 0, 0, -2 * s * x, 0, 0, s * x * x - 1.0])
+    qs = np.array(qs, np.float32)
+    nq = len(qs)
+    rng = np.random.default_rng(2)
+    n = 1500
+    P = np.zeros((n, 3), np.float32)
+    P[n // 2:] = (rng.normal(size=(n - n // 2, 3)) * 10.0 ** rng.uniform(-1, 5, (n - n // 2, 1))).astype(np.float32)
+    d = np.array([1.0, 0, 0]) + rng.normal(size=(n, 3)) * 10.0 ** rng.uniform(-4, -0.5, (n, 1))
+    d = np.ascontiguousarray(unit(d))
+    hits = np.zeros((n, nq), bool)
+    for kq in range(nq):
+        h, t = isect(o, np.ascontiguousarray(qs[kq]), P, d)
+        hits[:, kq] = h & (t > 0) & np.isfinite(t)
+    visited = np.zeros((n, nq), np.uint8)
+    n_idx = lib.rt_dbg_qindex_visit(_f(np.ascontiguousarray(qs)), nq, _f(P), _f(d), n, 0, None, visited.ctypes.data_as(C.POINTER(C.c_ubyte)))
+    assert n_idx == nq                                       # all indexed, hierarchy built (depth within the limit)
+    assert not (hits & (visited == 0)).any()
+    assert hits.sum() > n
