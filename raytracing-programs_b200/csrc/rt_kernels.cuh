@@ -862,12 +862,9 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
       } else {
         // shadow rays: only the spheres listed in the cell of the light buffer that the direction
         // from the light to P falls in (level by |P - L|; beyond the last level: every sphere)
-        for (unsigned m = alive & ~(r_on ? 1u : 0u); m; m &= m - 1) {
-          const int j = __ffs(m) - 1;
-          const int l = pass * LB + (int)((lmap >> (4 * (j - (r_on ? 1 : 0)))) & 15ull);
+        auto shadow_query = [&](const v3 Pq, const v3 dj, const int l, const int osph) -> bool {
           const float4 lp = sc.lights[4 * l];
-          const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
-          const float wx = lp.x - P.x, wy = lp.y - P.y, wz = lp.z - P.z;
+          const float wx = lp.x - Pq.x, wy = lp.y - Pq.y, wz = lp.z - Pq.z;
           const float q = __fmaf_rn(wz, wz, __fmaf_rn(wy, wy, wx * wx));
           int lv = -1;
           #pragma unroll
@@ -881,16 +878,25 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
               const int ss = sc.lb_items[k];
               const float4 hh = sc.lb_hot[k];                   // the sphere's filter operands, stored with the list
               o_sph++; d_sph++;
-              if (ss != obj_sph) occl = shadow_hits_sphere(sc, P, dj, ss, hh, n_cand);   // C/raycast.c:450
+              if (ss != osph) occl = shadow_hits_sphere(sc, Pq, dj, ss, hh, n_cand);   // C/raycast.c:450
             }
           } else {
             unsigned nt = 0;
             float bt = RT_INF;
             int bi = -1;
-            occl = bvh_trace<true>(sc, P, dj, obj_sph, bt, bi, n_cand, nt);
+            occl = bvh_trace<true>(sc, Pq, dj, osph, bt, bi, n_cand, nt);
             o_sph += nt; d_sph += nt;
           }
-          if (occl) alive &= ~(1u << j);
+          return occl;
+        };
+        // (dealing the warp's (hit point, ray) pairs out over its lanes by shuffle -- to even out the lanes' different
+        // numbers of live shadow rays -- was tried and dropped: 425 instead of 279 ms on C4, the owner look-up and the
+        // loss of per-lane locality cost more than the idle lanes)
+        for (unsigned m = alive & ~(r_on ? 1u : 0u); m; m &= m - 1) {
+          const int j = __ffs(m) - 1;
+          const int l = pass * LB + (int)((lmap >> (4 * (j - (r_on ? 1 : 0)))) & 15ull);
+          const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
+          if (shadow_query(P, dj, l, obj_sph)) alive &= ~(1u << j);
         }
         // reflection ray: nearest hit through the bounding-sphere hierarchy
         if (r_on) {
