@@ -74,7 +74,13 @@ __host__ __device__ inline int lb_cell(float ux, float uy, float uz) {
   else if (ay >= az) { m = ay; s = ux; t = uz; face = uy < 0.0f ? 3 : 2; }
   else { m = az; s = ux; t = uy; face = uz < 0.0f ? 5 : 4; }
   if (!(m > 0.0f) || !(m < 3.0e38f)) return -1;
+#ifdef __CUDA_ARCH__
+  // one approximate reciprocal instead of two IEEE divisions: its 2 ulp are nothing next to the 3e-4 rad the host adds to every cell
+  const float inv = __fdividef(1.0f, m);
+  int i = (int)floorf((s * inv + 1.0f) * (0.5f * RT_LB_RES)), j = (int)floorf((t * inv + 1.0f) * (0.5f * RT_LB_RES));
+#else
   int i = (int)floorf((s / m + 1.0f) * (0.5f * RT_LB_RES)), j = (int)floorf((t / m + 1.0f) * (0.5f * RT_LB_RES));
+#endif
   i = i < 0 ? 0 : i > RT_LB_RES - 1 ? RT_LB_RES - 1 : i;
   j = j < 0 ? 0 : j > RT_LB_RES - 1 ? RT_LB_RES - 1 : j;
   return (face * RT_LB_RES + j) * RT_LB_RES + i;
