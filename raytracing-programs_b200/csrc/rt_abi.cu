@@ -772,14 +772,22 @@ int rt_scene_upload(const rt_scene *scene) {
     quad_order.swap(reordered);
   }
   const int n_qidx = qi.n_idx;
-  LightBuffer cam, camq;                  // the cube map of the primary rays (apex = the camera), spheres and ellipsoids
-  // (usable only if its one level was really built: a scene of absurd extent leaves caps[0] at -1 and no lists)
-  const bool have_cam = have_lb && n_sph_real > 0 && !getenv("RT_NO_CAMGRID") && build_light_buffer(nullptr, sph, n_sph_real, nullptr, cam) &&
-                        cam.caps[0] >= 0.f;
-  const bool have_camq = have_lb && qi.n_idx > 0 && !getenv("RT_NO_CAMGRID") && build_light_buffer(nullptr, qi.slot_ball, qi.n_idx, &qi.slot_q, camq) &&
-                         camq.caps[0] >= 0.f;
-  LightBuffer lbq;                        // the same cube maps over the indexed ellipsoids
-  const bool have_lbq = n_qidx > 0 && !getenv("RT_NO_QLB") && build_light_buffer(scene, qi.slot_ball, n_qidx, &qi.slot_q, lbq);
+  // the cube map of the primary rays (apex = the camera) over spheres and ellipsoids -- usable only if its one level
+  // was really built: a scene of absurd extent leaves caps[0] at -1 and no lists -- and the light buffer over the
+  // indexed ellipsoids; the three builds are independent, one host thread each (plus one per light inside)
+  LightBuffer cam, camq, lbq;
+  bool have_cam = false, have_camq = false, have_lbq = false;
+  {
+    const bool camgrid = !getenv("RT_NO_CAMGRID"), qlb = !getenv("RT_NO_QLB");
+    std::thread t_cam([&] {
+      have_cam = have_lb && n_sph_real > 0 && camgrid && build_light_buffer(nullptr, sph, n_sph_real, nullptr, cam) && cam.caps[0] >= 0.f;
+    });
+    std::thread t_camq([&] {
+      have_camq = have_lb && n_qidx > 0 && camgrid && build_light_buffer(nullptr, qi.slot_ball, n_qidx, &qi.slot_q, camq) && camq.caps[0] >= 0.f;
+    });
+    std::thread t_lbq([&] { have_lbq = n_qidx > 0 && qlb && build_light_buffer(scene, qi.slot_ball, n_qidx, &qi.slot_q, lbq); });
+    t_cam.join(); t_camq.join(); t_lbq.join();
+  }
   const SphereBvh &qbvh = qi.bvh;
   const std::vector<float4> &qbvh_marg = qi.marg;
   const float q_behind_rel = qi.behind_rel;
