@@ -152,6 +152,9 @@ int rt_dbg_qindex_prune(const float *node4, const float *P3, const float *d3, in
  * Returns the number of indexed quadrics, -1 on bad arguments. */
 int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const float *d3, int n_rays, int nearest,
                         const float *best_t, unsigned char *visited);
+/* Sizes of the sphere light buffer rt_scene_upload would build for this scene: per_level[num_lights * 6] list
+ * entries per (light, distance level), -1 for a level that is not built; returns the total, -1 if there is none. */
+long long rt_dbg_light_buffer_sizes(const rt_scene *scene, long long *per_level);
 long long rt_dbg_qindex_last_nodes(void);   /* hierarchy nodes tested by the last rt_dbg_qindex_visit call */
 
 /* Flatten to type-sorted SoA (+ original index) and upload to every device in use.

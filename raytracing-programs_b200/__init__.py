@@ -63,7 +63,7 @@ ABI_SYMBOLS = ("rt_init", "rt_init_device", "rt_device_count", "rt_shutdown", "r
                "rt_abi_version", "rt_scene_upload", "rt_render", "rt_render_device", "rt_render_rank",
                "rt_assemble_device", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows",
                "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel", "rt_set_max_depth",
-               "rt_dbg_qindex_classify", "rt_dbg_qindex_prune", "rt_dbg_qindex_visit", "rt_dbg_qindex_last_nodes")
+               "rt_dbg_qindex_classify", "rt_dbg_qindex_prune", "rt_dbg_qindex_visit", "rt_dbg_qindex_last_nodes", "rt_dbg_light_buffer_sizes")
 
 _lib = None
 _host = None

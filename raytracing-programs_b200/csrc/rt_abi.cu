@@ -178,7 +178,7 @@ void warm_modules() {
 // if its float discriminant is >= 0, which by the reject-filter contract needs the line
 // to pass within r_eff = sqrt(r^2 + 2^-18 (T + r^2)) of C, T = |P - C|^2 (the filter's error budget of
 // 35u (T + r^2) plus the roundings of restating it in exact arithmetic: 59u < 2^-18); for |P - L| <= Dcap,
-// T <= (Dcap + |C - L|)^2.  So per light, per distance level (Dcap = 0.35 .. 32 x the light's scene
+// T <= (Dcap + |C - L|)^2.  So per light, per distance level (Dcap = 0.35 .. 16 x the light's scene
 // radius: the nearer the hit point, the less the spheres need inflating) and per cube-map cell the list holds every sphere whose cone of half-angle
 // asin(r_eff / |C - L|) around +-(C - L), widened by the cell's own angular radius and a 3e-4 rad
 // margin (float rounding of the direction and of the cell lookup is ~1e-7), meets the cell.
@@ -424,7 +424,10 @@ bool build_light_buffer(const rt_scene *scene, const std::vector<float4> &sph, i
       if (std::isfinite(d)) Rl = std::max(Rl, d);
     }
     if (!(Rl > 0) || !(Rl < 1e15)) return;
-    const double mult[RT_LB_LEVELS] = {0.35, 0.7, 1.4, 2.8, 8.0, 32.0};
+    // (the last level used to reach 32 x: its inflated spheres filled 25-58 cells' worth of list per cell and were 70 % of
+    // all entries; the few hit points beyond 16 x walk the hierarchy instead)
+    double mult[RT_LB_LEVELS] = {0.35, 0.7, 1.4, 2.8, 6.0, 16.0};
+    if (const char *e = getenv("RT_LB_FAR")) { double x = 0, y = 0; if (sscanf(e, "%lf,%lf", &x, &y) == 2 && x > 2.8 && y > x) { mult[4] = x; mult[5] = y; } }
     float capf[RT_LB_LEVELS];
     for (int lv = 0; lv < RT_LB_LEVELS; lv++) {
       const double Dcap = camera ? 0.0 : Rl * mult[lv];
@@ -574,6 +577,25 @@ int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const
     }
   }
   return qi.n_idx;
+}
+
+long long rt_dbg_light_buffer_sizes(const rt_scene *scene, long long *per_level) {
+  if (!scene || scene->num_lights <= 0) return -1;
+  std::vector<float4> sph;
+  for (int i = 0; i < scene->num_shapes; i++) {
+    const rt_shape &s = scene->shapes[i];
+    if (s.type == RT_SPHERE) sph.push_back(make_float4(s.position[0], s.position[1], s.position[2], s.params[0]));
+  }
+  LightBuffer lb;
+  if (sph.empty() || !build_light_buffer(scene, sph, (int)sph.size(), nullptr, lb)) return -1;
+  const size_t CELLS = (size_t)6 * RT_LB_RES * RT_LB_RES;
+  long long total = 0;
+  for (int g = 0; g < scene->num_lights * RT_LB_LEVELS; g++) {
+    const long long n = (long long)lb.start[(size_t)(g + 1) * CELLS] - (long long)lb.start[(size_t)g * CELLS];
+    if (per_level) per_level[g] = lb.caps[g] >= 0.f ? n : -1;
+    total += n;
+  }
+  return total;
 }
 
 int rt_set_accel(int mode) {
