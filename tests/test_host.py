@@ -239,3 +239,20 @@ def test_binary_writers_match_reference(tmp_path):
         for fn in ("ppm_WriteOutP6", "ppm_WriteOutP7"):
             assert _write_with(h, fn, W, H, 4, rgba, tmp_path / "a.ppm") == \
                 _write_with(r, fn, W, H, 4, rgba, tmp_path / "r.ppm"), (fn, W, H)
+
+
+def test_light_buffer_sizes_diagnostic():
+    """rt_dbg_light_buffer_sizes builds the sphere light buffer on the host (no GPU): six levels per light, list
+    sizes growing with the distance level (farther hit points need more inflated spheres), and none without spheres."""
+    lib = pkg.load_library()
+    lib.rt_dbg_light_buffer_sizes.restype = C.c_longlong
+    lib.rt_dbg_light_buffer_sizes.argtypes = [C.POINTER(pkg.RtScene), C.POINTER(C.c_longlong)]
+    sc = pkg.load_scene(os.path.join(rtlib.ROOT, "scenes", "c4_syn1032.scene"))
+    per = (C.c_longlong * (sc.num_lights * 6))()
+    total = lib.rt_dbg_light_buffer_sizes(C.byref(sc), per)
+    a = np.array(list(per)).reshape(sc.num_lights, 6)
+    assert total == a.sum() and (a > 0).all()
+    assert (np.diff(a, axis=1) >= 0).all()
+    assert 1.0 < a[:, 0].mean() / 6144 < 4.0                   # a few spheres per cell for nearby hit points
+    sc2 = pkg.load_scene(scene_path("quadric"))                 # 1 sphere
+    assert lib.rt_dbg_light_buffer_sizes(C.byref(sc2), None) > 0
