@@ -165,7 +165,10 @@ int rt_scene_upload(const rt_scene *scene);
 /* The raycast() body (C/raycast.c:109-129): render W x H, rows interleaved in bands of
  * rt band height over the GPUs in use, bands gathered to GPU 0 (NCCL when n_gpus > 1),
  * then copied to the HOST buffer rgb_out (3*W*H bytes, row-major, row 0 = top, no
- * padding: the pixmap of PPMFormat, C/ppm.h:6-12, with size_t instead of int sizes). */
+ * padding: the pixmap of PPMFormat, C/ppm.h:6-12, with size_t instead of int sizes).
+ * With n_gpus > 1 and rgb_out in pinned / registered memory there is no gather: every GPU
+ * copies its own bands to their places in rgb_out over its own PCIe link (the frame is then
+ * not left on GPU 0; env RT_HOST_GATHER=1 keeps the gather). */
 int rt_render(int width, int height, uint8_t *rgb_out, rt_stats *stats);
 
 /* Same render, result left in device memory of GPU 0 (inputs resident, no D2H):
@@ -177,15 +180,25 @@ int rt_render_device(int width, int height, void **dev_rgb_out, rt_stats *stats)
  * `nranks` on this process's device into dev_dst (caller-owned device memory of at least
  * 3*W*rt_rank_num_rows() bytes) or, when dev_dst is NULL, into a library-owned buffer;
  * the rank's rows lie back to back (band order). The caller gathers the rank
- * buffers with its own collective and de-interleaves with rt_band_rows(). */
+ * buffers with its own collective and de-interleaves with rt_rank_rows() / rt_assemble_device().
+ * dev_dst must be 4-byte aligned (checked: k_finalize stores 32-bit words). */
 int rt_render_rank(int width, int height, int rank, int nranks, void *dev_dst,
                    void **dev_rows_out, size_t *nbytes, rt_stats *stats);
 
 /* De-interleave gathered rank buffers (rank r's rows start at dev_staging +
  * rank_offsets[r], device memory of this process's device) into the row-major frame
- * dev_frame (3*W*H bytes). What rank 0 runs after its gather collective. */
+ * dev_frame (3*W*H bytes). What rank 0 runs after its gather collective.  When 3*W is a
+ * multiple of 16 the copy moves 16 bytes at a time: dev_frame and every dev_staging +
+ * rank_offsets[r] must then be 16-byte aligned (checked, RT_ERR_ARG otherwise). */
 int rt_assemble_device(int width, int height, int nranks, const void *dev_staging,
                        const int64_t *rank_offsets, void *dev_frame);
+
+/* Rows of `rank` (back to back in dev_rows, as rt_render_rank leaves them) copied straight to their places in the
+ * row-major HOST frame (3*W*H bytes, ideally pinned or cudaHostRegister'ed): a band of full-width rows is contiguous
+ * on both sides, so this is one strided copy per rank.  With one process per GPU and the host frame in shared
+ * memory, every rank moves its own bands over its own PCIe link instead of rank 0 copying the whole frame; the same
+ * routine serves rt_render when n_gpus > 1 and rgb_out is pinned.  Synchronous. */
+int rt_rank_rows_to_host(int width, int height, int rank, int nranks, const void *dev_rows, uint8_t *host_frame);
 
 /* Row ownership helpers shared by library, host and tests: band b = rows
  * [b*band_h, min((b+1)*band_h, H)) belongs to rank b % nranks. */

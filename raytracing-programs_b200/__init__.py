@@ -61,7 +61,7 @@ P3_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p)
 
 ABI_SYMBOLS = ("rt_init", "rt_init_device", "rt_device_count", "rt_shutdown", "rt_last_error",
                "rt_abi_version", "rt_scene_upload", "rt_render", "rt_render_device", "rt_render_rank",
-               "rt_assemble_device", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows",
+               "rt_assemble_device", "rt_rank_rows_to_host", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows",
                "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel", "rt_set_max_depth",
                "rt_dbg_qindex_classify", "rt_dbg_qindex_prune", "rt_dbg_qindex_visit", "rt_dbg_qindex_last_nodes", "rt_dbg_light_buffer_sizes")
 
@@ -87,6 +87,7 @@ def load_library():
                                    C.POINTER(C.c_size_t), C.POINTER(RtStats)]
     lib.rt_assemble_device.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p,
                                        C.POINTER(C.c_int64), C.c_void_p]
+    lib.rt_rank_rows_to_host.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     lib.rt_rank_num_rows.restype = C.c_int64
     lib.rt_rank_num_rows.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.rt_rank_rows.restype = C.c_int64
@@ -190,6 +191,11 @@ class Renderer:
         arr = (C.c_int64 * len(offsets))(*offsets)
         _check(self.lib, self.lib.rt_assemble_device(width, height, nranks, C.c_void_p(staging_ptr), arr,
                                                      C.c_void_p(frame_ptr)), "rt_assemble_device")
+
+    def rank_rows_to_host(self, width, height, rank, nranks, dev_rows_ptr, host_frame_ptr):
+        """This rank's rows (device, band order) -> their places in the row-major host frame (pinned / registered)."""
+        _check(self.lib, self.lib.rt_rank_rows_to_host(width, height, rank, nranks, C.c_void_p(dev_rows_ptr),
+                                                       C.c_void_p(host_frame_ptr)), "rt_rank_rows_to_host")
 
     def p3_text(self, width, height, pixmap=None, max_color=255):
         """ppm_WriteOutP3 (C/ppm.c:168-184) on the GPU: the P3 file of `pixmap` (numpy uint8
