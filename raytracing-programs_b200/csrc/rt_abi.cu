@@ -811,6 +811,22 @@ int rt_scene_upload(const rt_scene *scene) {
     sph_idx.push_back(-2);
   }
   const int n_sph_real = (int)slot_count_spheres;
+  // Constant-bank image of the reject-filter operands (rt_scene.cuh, c_sph / c_prim): {cx, cy, cz, rho} with
+  // rho = fl(r^2) (1 + 2^-18) + 2^-19 (1 + 2^-16) |C|^2, evaluated in double and rounded UP to float, so the
+  // filter's margin can only grow; every other entry of the bank never passes (rho = -inf => kappa' = +inf).
+  // All spheres when they fit, else the leading whole chunks (the kernels scan the rest from global memory).
+  const int n_csph = n_sph_real <= RT_CSPH_CAP - 8 ? n_sph_real : ((RT_CSPH_CAP - 8) / RT_CHUNK) * RT_CHUNK;
+  std::vector<float4> csph(RT_CSPH_CAP, make_float4(0.f, 0.f, 0.f, -INFINITY));
+  std::vector<float> cprim(RT_CSPH_CAP, -INFINITY);
+  for (int k = 0; k < n_csph; k++) {
+    const float4 h = sph_hot[k];
+    const double c2 = (double)h.x * h.x + (double)h.y * h.y + (double)h.z * h.z;
+    const double rho = (double)h.w * (1.0 + 3.814697265625e-06) + 1.9073486328125e-06 * (1.0 + 1.52587890625e-05) * c2;
+    float rf = (float)rho;
+    if ((double)rf < rho) rf = nextafterf(rf, INFINITY);
+    csph[k] = make_float4(h.x, h.y, h.z, rf);   // NaN radius or centre: NaN rho, the test is false, as before
+    cprim[k] = sph_prim[k].w;
+  }
   // light buffer (opt-in: rt_set_accel(1) or RT_ACCEL=1)
   LightBuffer lb;
   const bool have_lb = have_bvh && nl > 0 && build_light_buffer(scene, sph, n_sph_real, nullptr, lb);
@@ -903,6 +919,8 @@ int rt_scene_upload(const rt_scene *scene) {
     if (d.scene_blob) { cudaFree(d.scene_blob); d.scene_blob = nullptr; }
     CK(cudaMalloc(&d.scene_blob, total));
     CK(cudaMemcpyAsync(d.scene_blob, blob.data(), total, cudaMemcpyHostToDevice, d.stream));
+    CK(cudaMemcpyToSymbolAsync(c_sph, csph.data(), sizeof(float4) * RT_CSPH_CAP, 0, cudaMemcpyHostToDevice, d.stream));
+    CK(cudaMemcpyToSymbolAsync(c_prim, cprim.data(), sizeof(float) * RT_CSPH_CAP, 0, cudaMemcpyHostToDevice, d.stream));
     CK(cudaStreamSynchronize(d.stream));
     char *b = (char *)d.scene_blob;
     DevScene &sc = d.sc;
@@ -937,6 +955,7 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.camq_items = have_camq ? (const int *)(b + secs[31].off) : nullptr;
     sc.n_qidx = n_qidx;
     sc.q_behind_rel = q_behind_rel;
+    sc.n_csph = getenv("RT_NO_CONST_SCAN") ? 0 : n_csph;   // debugging aid: force the global-operand loop
     sc.max_depth = g_max_depth;
     const int pr = prepare_kernels(d);
     if (pr != RT_OK) return pr;

@@ -16,6 +16,7 @@ struct DevScene {
   const float4 *sph;        // [n_spheres] {cx, cy, cz, r}
   const float4 *sph_hot;    // [n_spheres padded to 4] reject-filter operands {cx, cy, cz, fl(r*r)}; pads never pass
   const float4 *sph_prim;   // [n_spheres] primary-ray constants {0-cx, 0-cy, 0-cz, c} (origin is exactly 0)
+  int n_csph;               // sphere slots 0 .. n_csph-1 are (also) in c_sph / c_prim; padded to a multiple of 8 there
   const int *sph_idx;       // [n_spheres] original index
   const float4 *pln;        // [2*n_planes] {px,py,pz,0} {nx,ny,nz,0}
   const int *pln_idx;
@@ -62,6 +63,18 @@ struct DevScene {
 };
 #define RT_LB_RES 32
 #define RT_LB_LEVELS 6
+
+// Sphere reject-filter operands in __constant__ memory (the scene "staged into constant memory", north_star item 2).
+// Why constant memory and not L1-cached global loads: every thread of a warp scans the same sphere at the same time, so
+// an operand read from the constant bank arrives in a UNIFORM register, and an FFMA with a uniform operand reads two
+// register-file operands instead of three.  On B200 a three-register FFMA issues at 0.61 per clock and scheduler, the
+// uniform-operand form at 0.96 (tools/scan_shapes.cu, profiles/r02_scan_shapes.md) -- the round-1 scan was capped by
+// exactly that.  Slot order = sph_hot order.  Entry: {cx, cy, cz, rho}, rho = fl(r^2) (1 + 2^-18) + 2^-19 |C|^2 rounded
+// up (host, double); pads hold rho = -inf and never pass.  Scenes with more spheres than the bank holds scan the
+// remainder from global memory with the round-1 loop.
+#define RT_CSPH_CAP 2560
+__constant__ float4 c_sph[RT_CSPH_CAP];
+__constant__ float c_prim[RT_CSPH_CAP];   // primary rays (origin exactly 0): the filter constant of sph_prim[].w
 
 // Cube-map cell of direction u (any length): face = 2 * major axis + (negative ? 1 : 0), the other two
 // components divided by |major| map [-1, 1] onto RT_LB_RES cells.  Returns -1 for a zero or NaN vector.
