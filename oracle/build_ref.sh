@@ -31,6 +31,13 @@ gcc $CFLAGS "$TMP/raycast_patched.c" $SUPPORT -o "$OUT/raytrace_ref" -lm
 gcc $CFLAGS "$TMP/raycast_p1.c" $SUPPORT -o "$OUT/raytrace_asis" -lm
 gcc $CFLAGS -fPIC -shared -DREF_RAYCAST_C="\"$TMP/raycast_patched.c\"" \
     "$HERE/ref_harness.c" $SUPPORT -o "$OUT/libref.so" -lm -lpthread
+# Ray-counting variant (bench.py's reference arm counts the rays of its sample with the reference itself, untimed):
+# the call sites of find_nearest_object -- the only places where "find_nearest_object(json_struct," occurs -- go
+# through a counting macro of ref_harness.c.  Never used for timing.
+sed -e 's|find_nearest_object(json_struct,|ref_counted_fno(json_struct,|' "$TMP/raycast_patched.c" > "$TMP/raycast_count.c"
+[ "$(grep -c 'ref_counted_fno(json_struct,' "$TMP/raycast_count.c")" -ge 3 ] || { echo "count patch did not apply" >&2; exit 1; }
+gcc $CFLAGS -fPIC -shared -DREF_COUNT_RAYS -DREF_RAYCAST_C="\"$TMP/raycast_count.c\"" \
+    "$HERE/ref_harness.c" $SUPPORT -o "$OUT/libref_count.so" -lm -lpthread
 # Deep-bounce variant of the same harness: MAX_RECURSION 7 -> 50, the bound the reference's own CUDA and OptiX
 # variants use (CUDA/raycast.cu:13 MAX_ITER, Optix/src/deviceCode.cu:5); pins rt_set_max_depth(50).
 sed -e 's|^const int MAX_RECURSION = 7;$|const int MAX_RECURSION = 50;|' "$TMP/raycast_patched.c" > "$TMP/raycast_d50.c"

@@ -13,9 +13,19 @@
  * Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may load the
  * resulting oracle/_ref/libref.so.
  */
+/* libref_count.so only (-DREF_COUNT_RAYS, never the timed library): build_ref.sh rewrites the three live CALL SITES of
+ * find_nearest_object (C/raycast.c:325,357,401) to ref_counted_fno, which counts the call -- "rays" in the bench
+ * metric are exactly these calls -- and forwards it unchanged. */
+#ifdef REF_COUNT_RAYS
+static unsigned long long ref_ray_calls;
+#define ref_counted_fno(...) (__atomic_fetch_add(&ref_ray_calls, 1ull, __ATOMIC_RELAXED), find_nearest_object(__VA_ARGS__))
+#endif
 #define main ref_main
 #include REF_RAYCAST_C
 #undef main
+#ifdef REF_COUNT_RAYS
+unsigned long long ref_ray_count_reset(void) { return __atomic_exchange_n(&ref_ray_calls, 0ull, __ATOMIC_RELAXED); }
+#endif
 
 #include <pthread.h>
 

@@ -86,8 +86,8 @@ struct DeviceCtx {
   // P3 writer (device 0 only)
   char *p3_text = nullptr; size_t p3_text_cap = 0;
   unsigned long long *p3_state = nullptr; size_t p3_state_cap = 0;   // span offsets + span lengths (bytes)
-  char *p3_pinned[2] = {nullptr, nullptr}; size_t p3_pinned_cap = 0;
-  cudaEvent_t p3_ev[2] = {nullptr, nullptr};
+  char *p3_pinned[3] = {nullptr, nullptr, nullptr}; size_t p3_pinned_cap = 0;   // three slabs: copy k+2 is queued while the sink has k
+  cudaEvent_t p3_ev[3] = {nullptr, nullptr, nullptr};
   int frame_w = 0, frame_h = 0;   // size of the frame currently held in `frame`
 };
 
@@ -167,7 +167,7 @@ void free_device(DeviceCtx &d) {
   cudaFree(d.scene_blob); cudaFree(d.acc); /* c0, qbuf, qcls live in the same block */ cudaFree(d.qcount);
   cudaFree(d.counters); cudaFree(d.rank_buf); cudaFree(d.staging); cudaFree(d.frame);
   cudaFree(d.p3_text); cudaFree(d.p3_state);
-  for (int k = 0; k < 2; k++) { if (d.p3_pinned[k]) cudaFreeHost(d.p3_pinned[k]); if (d.p3_ev[k]) cudaEventDestroy(d.p3_ev[k]); }
+  for (int k = 0; k < 3; k++) { if (d.p3_pinned[k]) cudaFreeHost(d.p3_pinned[k]); if (d.p3_ev[k]) cudaEventDestroy(d.p3_ev[k]); }
   if (d.ev0) cudaEventDestroy(d.ev0);
   if (d.ev1) cudaEventDestroy(d.ev1);
   if (d.ev2) cudaEventDestroy(d.ev2);
@@ -801,9 +801,9 @@ int rt_scene_upload(const rt_scene *scene) {
     if (getenv("RT_NO_CULL")) cull_ok = false;   // debugging aid: trace every shadow ray
     lights[4 * l + 3] = make_float4(t.direction[0], t.direction[1], t.direction[2], cull_ok ? 1.0f : 0.0f);
   }
-  // pad the per-sphere arrays to a multiple of 4 with entries the reject filter never passes
+  // pad the per-sphere arrays to a multiple of 32 with entries the reject filter never passes
   // (r*r = -inf => k = -inf) so the hot loops can run unrolled without a tail
-  const size_t padded = (sph_hot.size() + 3) / 4 * 4 + 4;   // + one prefetch group
+  const size_t padded = (sph_hot.size() + 31) / 32 * 32 + 4;   // whole 32-sphere words (the scans record survivors per word) + one prefetch group
   while (sph_hot.size() < padded) {
     sph_hot.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));
     sph.push_back(make_float4(0.f, 0.f, 0.f, 0.f));
@@ -815,7 +815,8 @@ int rt_scene_upload(const rt_scene *scene) {
   // rho = fl(r^2) (1 + 2^-18) + 2^-19 (1 + 2^-16) |C|^2, evaluated in double and rounded UP to float, so the
   // filter's margin can only grow; every other entry of the bank never passes (rho = -inf => kappa' = +inf).
   // All spheres when they fit, else the leading whole chunks (the kernels scan the rest from global memory).
-  const int n_csph = n_sph_real <= RT_CSPH_CAP - 8 ? n_sph_real : ((RT_CSPH_CAP - 8) / RT_CHUNK) * RT_CHUNK;
+  // (the scan reads whole 32-sphere words and prefetches one trip ahead: 40 spare entries)
+  const int n_csph = n_sph_real <= RT_CSPH_CAP - 40 ? n_sph_real : ((RT_CSPH_CAP - 40) / RT_CHUNK) * RT_CHUNK;
   std::vector<float4> csph(RT_CSPH_CAP, make_float4(0.f, 0.f, 0.f, -INFINITY));
   std::vector<float> cprim(RT_CSPH_CAP, -INFINITY);
   for (int k = 0; k < n_csph; k++) {
@@ -1513,15 +1514,23 @@ int rt_p3_write(const uint8_t *host_rgb, int W, int H, unsigned max_color, rt_p3
   trace("rt_p3_write: begin");
   if ((r = dev_realloc(d.p3_text, d.p3_text_cap, rt_p3_max_bytes(W, H) + 64)) != RT_OK) return r;
   trace("rt_p3_write: text buffer allocated");
-  const size_t slab = (size_t)32 << 20;
+  // Pinned staging slabs sized to the job: pinning costs ~0.4 ms per MiB (the round-1 writer pinned 64 MiB up front,
+  // 25 ms of a 30 ms one-shot 1000x1000 run), a big frame wants large slabs to keep the PCIe link busy.  Three of
+  // them, each 1/6 of the worst-case text, between 1 and 64 MiB.
+  size_t slab = rt_p3_max_bytes(W, H) / 6;
+  slab = (slab + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+  if (slab < ((size_t)1 << 20)) slab = (size_t)1 << 20;
+  if (slab > ((size_t)64 << 20)) slab = (size_t)64 << 20;
   if (d.p3_pinned_cap < slab) {
-    for (int k = 0; k < 2; k++) {
+    for (int k = 0; k < 3; k++) {
+      if (d.p3_pinned[k]) { CK(cudaFreeHost(d.p3_pinned[k])); d.p3_pinned[k] = nullptr; }
       CK(cudaHostAlloc((void **)&d.p3_pinned[k], slab, cudaHostAllocDefault));
-      CK(cudaEventCreateWithFlags(&d.p3_ev[k], cudaEventDisableTiming));
+      if (!d.p3_ev[k]) CK(cudaEventCreateWithFlags(&d.p3_ev[k], cudaEventDisableTiming));
     }
     d.p3_pinned_cap = slab;
     trace("rt_p3_write: pinned slabs allocated");
   }
+  slab = d.p3_pinned_cap;
   CK(cudaEventRecord(d.ev0, d.stream));
   size_t n_spans = 0;
   if ((r = p3_enqueue(d, d.frame, W, H, max_color, d.p3_text, &n_spans)) != RT_OK) return r;
@@ -1530,20 +1539,21 @@ int rt_p3_write(const uint8_t *host_rgb, int W, int H, unsigned max_color, rt_p3
   trace("rt_p3_write: text formatted on the GPU");
   unsigned long long total = 0;
   CK(cudaMemcpy(&total, d.p3_state + n_spans, sizeof total, cudaMemcpyDeviceToHost));
-  // text -> host through two pinned slabs: the copy of slab k+1 overlaps the sink of slab k
+  // text -> host through the pinned slabs: copies k+1 and k+2 are in flight while the sink consumes slab k
   const size_t n_slabs = ((size_t)total + slab - 1) / slab;
   int sink_rc = 0;
-  for (size_t k = 0; k <= n_slabs && !sink_rc; k++) {
-    if (k < n_slabs) {
-      const size_t off = k * slab, nb = (size_t)total - off < slab ? (size_t)total - off : slab;
-      CK(cudaMemcpyAsync(d.p3_pinned[k & 1], d.p3_text + off, nb, cudaMemcpyDeviceToHost, d.stream));
-      CK(cudaEventRecord(d.p3_ev[k & 1], d.stream));
-    }
-    if (k > 0) {
-      const size_t off = (k - 1) * slab, nb = (size_t)total - off < slab ? (size_t)total - off : slab;
-      CK(cudaEventSynchronize(d.p3_ev[(k - 1) & 1]));
-      sink_rc = sink(d.p3_pinned[(k - 1) & 1], nb, user);
-    }
+  auto enqueue_copy = [&](size_t k) -> int {
+    const size_t off = k * slab, nb = (size_t)total - off < slab ? (size_t)total - off : slab;
+    CK(cudaMemcpyAsync(d.p3_pinned[k % 3], d.p3_text + off, nb, cudaMemcpyDeviceToHost, d.stream));
+    CK(cudaEventRecord(d.p3_ev[k % 3], d.stream));
+    return RT_OK;
+  };
+  for (size_t k = 0; k < 2 && k < n_slabs; k++) if ((r = enqueue_copy(k)) != RT_OK) return r;
+  for (size_t k = 0; k < n_slabs && !sink_rc; k++) {
+    if (k + 2 < n_slabs && (r = enqueue_copy(k + 2)) != RT_OK) return r;   // slab (k+2)%3 was consumed at step k-1
+    const size_t off = k * slab, nb = (size_t)total - off < slab ? (size_t)total - off : slab;
+    CK(cudaEventSynchronize(d.p3_ev[k % 3]));
+    sink_rc = sink(d.p3_pinned[k % 3], nb, user);
   }
   CK(cudaStreamSynchronize(d.stream));
   trace("rt_p3_write: text delivered to the sink");

@@ -23,10 +23,13 @@
 #define RT_SCAN4_MAX 0   /* scan variants up to this many slots take 4 spheres per loop trip, wider ones 2 */
 #endif
 #ifndef RT_TRIP1_MIN
-#define RT_TRIP1_MIN 15  /* constant-bank scan: variants with >= this many slots take 1 sphere per loop trip, */
+#define RT_TRIP1_MIN 13  /* constant-bank scan: variants with >= this many slots take 1 sphere per loop trip, */
+#endif
+#ifndef RT_PREFETCH2
+#define RT_PREFETCH2 0
 #endif
 #ifndef RT_TRIP2_MIN
-#define RT_TRIP2_MIN 9   /* >= this many 2, narrower ones 4 */
+#define RT_TRIP2_MIN 5   /* >= this many 2, narrower ones 4 */
 #endif
 #define RT_CHUNK 128     /* spheres per scan chunk = capacity of the per-thread survivor queue */
 #define RT_INF __int_as_float(0x7f800000)
@@ -66,7 +69,7 @@ RT_DEV int warp_agg_add(int *counter) {
 // Same rule as k_shade's ray setup, but on the un-normalised light vector and without
 // caring about rounding: a wrong guess only costs balance, never correctness.
 RT_DEV int hit_class(const DevScene &sc, v3 P, v3 N, int obj, bool can_reflect, int nr_max) {
-  if (nr_max <= 5) return RT_NCLS - 1;   // one scan variant only: nothing to sort
+  if (nr_max < 3 + RT_VSTEP) return 0;    // one scan variant only: nothing to sort
   const float refl = sc.mat[2 * obj].w, opacity = sc.mat[2 * obj + 1].w;
   int cnt = (can_reflect && refl > 0.0f) ? 1 : 0;
   if (opacity > 0.0f) {
@@ -77,8 +80,12 @@ RT_DEV int hit_class(const DevScene &sc, v3 P, v3 N, int obj, bool can_reflect, 
       cnt += (sc.lights[4 * l + 3].w == 0.0f || !(s <= 0.0f)) ? 1 : 0;
     }
   }
-  // classes follow the scan variants of k_shade: <= nr-12, <= nr-8, <= nr-4, <= nr
-  return cnt <= nr_max - 12 ? 0 : cnt <= nr_max - 8 ? 1 : cnt <= nr_max - 4 ? 2 : 3;
+  // one class per scan variant of k_shade (nr_max, nr_max - RT_VSTEP, ... >= 3 slots), the narrowest = class 0
+  const int vmin = nr_max - RT_VSTEP * ((nr_max - 3) / RT_VSTEP);
+  int v = nr_max - RT_VSTEP * ((nr_max - cnt) / RT_VSTEP);
+  if (v < vmin) v = vmin;
+  const int c = (v - vmin) / RT_VSTEP;
+  return c < RT_NCLS ? c : RT_NCLS - 1;
 }
 
 // Appends one entry per lane that has `on` set.  Called by ALL 32 lanes in converged code (full-mask collectives, no
@@ -373,10 +380,12 @@ __device__ __noinline__ void resolve_spheres(const float (*dsm)[128], const int 
                                              const unsigned w0, const unsigned w1, const unsigned w2, const unsigned w3,
                                              const int obj, const bool r_on,
                                              unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
-  // survivors of the chunk: one bit per sphere, 32 spheres per word; w0 is the LAST word scanned (word nw-1), w1 the one before, ...
+  // survivors of the chunk: one bit per sphere, 32 spheres per word, the first sphere of a word in bit 31 (the scans shift
+  // their bits in from the right); w0 is the LAST word scanned (word nw-1), w1 the one before, ...
   for (int k = nw - 1; k >= 0; k--)
-  for (unsigned sm = k == 0 ? w0 : k == 1 ? w1 : k == 2 ? w2 : w3; sm; sm &= sm - 1) {
-    const int ss = cs + ((nw - 1 - k) << 5) + __ffs(sm) - 1;
+  for (unsigned sm = k == 0 ? w0 : k == 1 ? w1 : k == 2 ? w2 : w3; sm; sm &= ~(0x80000000u >> __clz(sm))) {
+    const int ss = cs + ((nw - 1 - k) << 5) + __clz(sm);
+    if (ss >= sc.n_spheres) continue;                          // a pad entry can only get here with a NaN margin (|P|^2 overflow)
     const int idx = sc.sph_idx[ss];
     if (idx == obj) continue;                                  // C/raycast.c:450
     const float4 hh = sc.sph_hot[ss];
@@ -455,10 +464,10 @@ RT_DEV void scan_chunk_g(const float (*dsm)[128], const int tid, const v3 P,
         mx0 = fmaxf(mx0, fabsf(__fmaf_rn(d[j].z, z0, __fmaf_rn(d[j].y, y0, d[j].x * x0))));
         mx1 = fmaxf(mx1, fabsf(__fmaf_rn(d[j].z, z1, __fmaf_rn(d[j].y, y1, d[j].x * x1))));
       }
-      wc |= (mx0 * mx0 >= ka0) ? (1u << s) : 0u;
-      wc |= (mx1 * mx1 >= ka1) ? (2u << s) : 0u;
+      wc = __funnelshift_l(__float_as_uint(__fmaf_rn(mx0, mx0, -ka0)), wc, 1);   // sign bit set = rejected (see scan_chunk_c)
+      wc = __funnelshift_l(__float_as_uint(__fmaf_rn(mx1, mx1, -ka1)), wc, 1);
     }
-    w3 = w2; w2 = w1; w1 = w0; w0 = wc;
+    w3 = w2; w2 = w1; w1 = w0; w0 = ~wc;
   }
   resolve_spheres(dsm, tid, P, sc, cs, nw, w0, w1, w2, w3, obj, r_on, alive, best_t, best_idx, n_cand);
 }
@@ -495,14 +504,29 @@ RT_DEV void scan_chunk_c(const float (*dsm)[128], const int tid, const v3 P, con
   constexpr int U = NRV >= RT_TRIP1_MIN ? 1 : NRV >= RT_TRIP2_MIN ? 2 : 4;
   unsigned w0 = 0, w1 = 0, w2 = 0, w3 = 0;
   const int nw = (n + 31) >> 5;                              // whole words: the bank is padded with entries that never pass
+  float4 gn[U];                                              // operands of the next trip, in flight during this one
+  #pragma unroll
+  for (int u = 0; u < U; u++) gn[u] = c_sph[cs + u];
+#if RT_PREFETCH2
+  float4 gn2[U];                                             // ... and of the one after (the constant load's latency is ~1 trip)
+  #pragma unroll
+  for (int u = 0; u < U; u++) gn2[u] = c_sph[cs + U + u];
+#endif
   #pragma unroll 1
   for (int w = 0; w < nw; w++) {
     unsigned wc = 0;
     #pragma unroll 1
     for (int s = 0; s < 32; s += U) {
+      float4 gc[U];
+      #pragma unroll
+#if RT_PREFETCH2
+      for (int u = 0; u < U; u++) { gc[u] = gn[u]; gn[u] = gn2[u]; gn2[u] = c_sph[cs + (w << 5) + s + 2 * U + u]; }
+#else
+      for (int u = 0; u < U; u++) { gc[u] = gn[u]; gn[u] = c_sph[cs + (w << 5) + s + U + u]; }   // warp-uniform index: uniform registers
+#endif
       #pragma unroll
       for (int u = 0; u < U; u++) {
-        const float4 g = c_sph[cs + (w << 5) + s + u];         // warp-uniform index: uniform registers
+        const float4 g = gc[u];
         const float x = P.x - g.x, y = P.y - g.y, z = P.z - g.z;
         const float T = __fmaf_rn(z, z, __fmaf_rn(y, y, x * x));
         const float ka = __fmaf_rn(T, 1.0f - RT_FILTER_EPS, -(g.w + p2s));
@@ -510,10 +534,12 @@ RT_DEV void scan_chunk_c(const float (*dsm)[128], const int tid, const v3 P, con
         #pragma unroll
         for (int j = 0; j < NRV; j++)
           m = fmaxf(m, fabsf(__fmaf_rn(nz[j], g.z, __fmaf_rn(ny[j], g.y, __fmaf_rn(nx[j], g.x, q[j])))));
-        wc |= (m * m >= ka) ? (1u << (s + u)) : 0u;
+        // survivor bit: the SIGN of m^2 - kappa' (one FFMA, exact sign) shifted into the word (one SHF) -- first sphere of
+        // the word ends up in bit 31, a set bit means REJECTED; a NaN kappa' gives a clear bit = survivor, resolved exactly
+        wc = __funnelshift_l(__float_as_uint(__fmaf_rn(m, m, -ka)), wc, 1);
       }
     }
-    w3 = w2; w2 = w1; w1 = w0; w0 = wc;
+    w3 = w2; w2 = w1; w1 = w0; w0 = ~wc;
   }
   resolve_spheres(dsm, tid, P, sc, cs, nw, w0, w1, w2, w3, obj, r_on, alive, best_t, best_idx, n_cand);
 }
@@ -836,7 +862,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
   // Dynamic scheduling: every warp claims 32 consecutive entries of one class list at a time
   // (heaviest class first), so no SM idles while another still holds a backlog, and the hit
   // points a warp shades together need about the same number of ray slots.
-  int cstart[RT_NCLS + 1];   // virtual index space: class lists padded to multiples of 32, class 3 first
+  int cstart[RT_NCLS + 1];   // virtual index space: class lists padded to multiples of 32, heaviest class first
   cstart[0] = 0;
   #pragma unroll
   for (int c = 0; c < RT_NCLS; c++) cstart[c + 1] = cstart[c] + ((qin.ctl[RT_NCLS - c] + 31) & ~31);
@@ -847,7 +873,7 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
   const int vend = __shfl_sync(0xffffffffu, cstart[RT_NCLS], 0);
   for (int claim_no = 0; claim_no <= qin.cap; claim_no++) {
     int vbase = 0;
-    if ((threadIdx.x & 31) == 0) vbase = atomicAdd(&qin.ctl[5], 32);
+    if ((threadIdx.x & 31) == 0) vbase = atomicAdd(&qin.ctl[RT_CTL_CURSOR], 32);
     vbase = __shfl_sync(0xffffffffu, vbase, 0);
     if (vbase >= vend) break;
     int c = 0;

@@ -105,16 +105,19 @@ __host__ __device__ inline int lb_cell(float ux, float uy, float uz) {
 // lists class by class, so the 32 hit points a warp shades together need about the same number
 // of ray slots.  The class is only a scheduling hint: the consumer sizes its scan from the
 // exact count it computes itself.
-#define RT_NCLS 4
+#ifndef RT_NCLS
+#define RT_NCLS 8     /* one class per scan variant of the widest kernel (17, 15, ... 3 ray slots) */
+#endif
 struct HitQueue {
   float4 *r0;   // P.xyz, pixel (tile-local index, int bits)
   float4 *r1;   // N.xyz, object (original index, int bits)
   float4 *r2;   // V.xyz (direction of the ray that made the hit), throughput
   int *cls;     // [RT_NCLS][cap] entry numbers per class
-  int *ctl;     // [0] entries, [1..RT_NCLS] entries per class, [5] work cursor of the consuming launch
+  int *ctl;     // [0] entries, [1..RT_NCLS] entries per class, [RT_CTL_CURSOR] work cursor of the consuming launch
   int cap;
 };
-#define RT_CTL_STRIDE 8
+#define RT_CTL_CURSOR (1 + RT_NCLS)
+#define RT_CTL_STRIDE 16
 
 // Device counters (unsigned long long each).
 enum {

@@ -14,9 +14,11 @@
  * split of the timed region.  RT_VERBOSE=1 adds the GPU-side statistics to that line,
  * RT_TRACE=1 wall-clock stamps of every host-side stage on stderr.
  */
+#define _GNU_SOURCE
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <sys/mman.h>
 #include <sys/time.h>
 #include "raycast_host.h"
 
@@ -62,7 +64,19 @@ int main(int argc, char **argv) {
   photo_data.width = width;
   const size_t bytes = (size_t)width * (size_t)height * 3u;
   photo_data.size = bytes > (size_t)INT32_MAX ? INT32_MAX : (int)bytes;
-  photo_data.pixmap = (uint8_t *)malloc(bytes);
+  /* malloc() as in C/raycast.c:53; large pixmaps are 2 MiB-aligned and marked for transparent huge pages, so that
+     the first touch (the device-to-host copy of the frame) takes 50 page faults per 100 MB instead of 25 000 */
+  photo_data.pixmap = NULL;
+  if (bytes >= ((size_t)4 << 20)) {
+    void *p = NULL;
+    if (posix_memalign(&p, (size_t)2 << 20, (bytes + (((size_t)2 << 20) - 1)) & ~(((size_t)2 << 20) - 1)) == 0) {
+#ifdef MADV_HUGEPAGE
+      madvise(p, bytes, MADV_HUGEPAGE);
+#endif
+      photo_data.pixmap = (uint8_t *)p;
+    }
+  }
+  if (photo_data.pixmap == NULL) photo_data.pixmap = (uint8_t *)malloc(bytes);
   if (photo_data.pixmap == NULL) {
     fprintf(stderr, "Error: Unable to allocate a %dx%d image.\n", width, height);
     exit(1);
