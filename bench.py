@@ -597,9 +597,10 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    rays_p, rays_r, rays_s, hitp, flops, launches, t_so, t_sd, t_qo, t_qd, t_slots = allsum(
+    rays_p, rays_r, rays_s, hitp, flops, launches, t_so, t_sd, t_qo, t_qd, t_slots, t_bo, t_bd = allsum(
         [agg.rays_primary, agg.rays_reflection, agg.rays_shadow, agg.hit_points, agg.flops, agg.kernel_launches,
-         agg.sphere_tests_o, agg.sphere_tests_d, agg.quadric_tests_o, agg.quadric_tests_d, agg.scan_slots])
+         agg.sphere_tests_o, agg.sphere_tests_d, agg.quadric_tests_o, agg.quadric_tests_d, agg.scan_slots,
+         agg.ball_tests_o, agg.ball_tests_d])
     rays = rays_p + rays_r + rays_s
     ms_step = allmax(dev_ms / args.steps)
     wall_step = allmax(wall_ms / args.steps)
@@ -650,8 +651,10 @@ def main():
            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 roots)", "data": "synthetic",
            "config": bench_config(name, W, H, sc.num_shapes, sc.num_lights, world),
            "workload_stats": {"rays_per_pixel": rays / (W * H), "rays": {"primary": rays_p, "reflection": rays_r, "shadow": rays_s},
-                              "scan": {"hit_points": hitp, "live_rays_per_primitive_scanned": (t_sd + t_qd) / max(t_so + t_qo, 1),
-                                       "slots_per_primitive_scanned": t_slots / max(t_so + t_qo, 1)}},
+                              "scan": {"hit_points": hitp, "live_rays_per_primitive_scanned": (t_sd + t_bd) / max(t_so + t_bo, 1),
+                                       "slots_per_primitive_scanned": t_slots / max(t_so + t_bo, 1),
+                                       "quadric_bounding_ball_tests": t_bo, "quadrics_past_their_ball": t_qo,
+                                       "quadric_filter_evaluations": t_qd}},
            "mpixels_per_s": W * H / ms_step / 1e3, "tflops_fp32_algorithmic": flops / ms_step / 1e9,
            "frac_fp32_peak": flops / ms_step / 1e9 / (pk["fp32_tflops"] * world),
            "roofline": roof, "e2e": e2e, "gpu_launches": int(launches * args.steps + (args.steps if world > 1 else 0)),

@@ -104,6 +104,8 @@ typedef struct rt_stats {
   double ms_total;              /* the whole call, host clock */
   uint64_t scan_slots;          /* ray slots x primitives the bundle scans executed (>= the *_tests_d sum:
                                    slots of rays already occluded, or padding, still ride along) */
+  uint64_t ball_tests_o, ball_tests_d;   /* bounding-ball pre-tests of the quadric scan (sphere-type tests: 10 + 8 flops);
+                                            quadric_tests_* then count only the quadrics that passed them */
 } rt_stats;
 
 /* Initialise n_gpus devices (0 = all visible). Safe to call again after rt_shutdown. */
@@ -120,6 +122,18 @@ int rt_abi_version(void);
  * (CUDA/raycast.cu:13,216); rt_set_max_depth(50) is that mode.  1..64, takes effect at
  * the next render.  Env RT_MAX_DEPTH in the CLI. */
 int rt_set_max_depth(int depth);
+
+/* Which of the reference's two tracers combines the hits of a pixel.
+ * RT_MODE_ITERATIVE (default): iterative_shoot, the live path (C/raycast.c:121,315-379): bounce colours weighted by
+ * the running product of reflectivities, summed bounce first, primary last.
+ * RT_MODE_SHOOT: the dormant recursive shoot() (C/raycast.c:152-296): out_k = colour_k + out_(k+1) * reflectivity_k
+ * from the deepest hit outwards.  Its refraction subtree is traced by the reference but never added to the colour
+ * (:293,295 are commented out), so the value depends on the reflection chain only: same hits, same shadow rays, a
+ * different order of the float operations (pixels differ from the live path in the 1e-6 range).  The discarded
+ * refraction rays are not traced here.  Takes effect at the next render.  Env RT_MODE=shoot in the CLI. */
+#define RT_MODE_ITERATIVE 0
+#define RT_MODE_SHOOT 1
+int rt_set_mode(int mode);
 
 /* Acceleration of the nearest-hit search, read by the next rt_scene_upload.
  * 0 (default): every ray tests every shape, as C/raycast.c:449 does.  1: the sphere part of shadow

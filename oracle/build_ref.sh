@@ -26,10 +26,11 @@ sed -e 's|^  json_struct->num_shapes = 0;$|  json_struct->num_shapes = 0; json_s
 grep -q 'next_nearest_object = NULL;' "$TMP/raycast_patched.c" || { echo "P2 patch did not apply" >&2; exit 1; }
 grep -q 'num_lights = 0;' "$TMP/raycast_patched.c" || { echo "P1 patch did not apply" >&2; exit 1; }
 CFLAGS="-O3 -ffp-contract=off -w -I$REF"
+HFLAGS="$CFLAGS -DNDEBUG"   # harness libraries: shoot()'s assert (C/raycast.c:245) off, see ref_harness.c
 SUPPORT="$REF/v3math.c $REF/ppm.c $REF/parse.c $REF/objects.c"
 gcc $CFLAGS "$TMP/raycast_patched.c" $SUPPORT -o "$OUT/raytrace_ref" -lm
 gcc $CFLAGS "$TMP/raycast_p1.c" $SUPPORT -o "$OUT/raytrace_asis" -lm
-gcc $CFLAGS -fPIC -shared -DREF_RAYCAST_C="\"$TMP/raycast_patched.c\"" \
+gcc $HFLAGS -fPIC -shared -DREF_RAYCAST_C="\"$TMP/raycast_patched.c\"" \
     "$HERE/ref_harness.c" $SUPPORT -o "$OUT/libref.so" -lm -lpthread
 # Ray-counting variant (bench.py's reference arm counts the rays of its sample with the reference itself, untimed):
 # the call sites of find_nearest_object -- the only places where "find_nearest_object(json_struct," occurs -- go

@@ -129,6 +129,39 @@ void ref_render_rows(void *h, int W, int H, int y0, int y1, uint8_t *out) {
   }
 }
 
+/* The same rows through the reference's dormant recursive tracer shoot() (C/raycast.c:152-296), called the way its
+ * doc comment says (recursion level MAX_RECURSION, skip -1).  Its refraction subtree runs too (and reads uninitialised
+ * memory when the inner ray misses, :214-221) but its result is never added to the colour (:293,295 are commented
+ * out), so the pixels do not depend on it.  Built with -DNDEBUG: the assert at :245 is float-rounding sensitive. */
+static int ref_use_shoot = 0;
+void ref_set_mode(int m) { ref_use_shoot = m ? 1 : 0; }
+static void ref_render_rows_shoot(void *h, int W, int H, int y0, int y1, uint8_t *out) {
+  ref_scene *s = (ref_scene *)h;
+  json_data_t *json_struct = &s->js;
+  int view_plane_center[3] = {0, 0, -1};
+  float ray_orgin[3] = {0, 0, 0};
+  float ray_direction[3];
+  float color[3];
+  uint8_t maxColor = 255;
+  float pixel_height = json_struct->camera_height / H;
+  float pixel_width = json_struct->camera_width / W;
+  uint8_t *pixel = out;
+  for (int y = y0; y < y1; y++) {
+    for (int x = 0; x < W; x++) {
+      ray_direction[0] = view_plane_center[0] - (json_struct->camera_width / 2.0) + pixel_width * (x + 0.5);
+      ray_direction[1] = view_plane_center[1] + (json_struct->camera_height / 2.0) - pixel_height * (y + 0.5);
+      ray_direction[2] = view_plane_center[2];
+      v3_normalize(ray_direction, ray_direction);
+      shoot(json_struct, ray_orgin, ray_direction, color, MAX_RECURSION, -1);
+      v3_scale(color, maxColor);
+      pixel[0] = ppm_clamp(color[0], 0, maxColor);
+      pixel[1] = ppm_clamp(color[1], 0, maxColor);
+      pixel[2] = ppm_clamp(color[2], 0, maxColor);
+      pixel += 3;
+    }
+  }
+}
+
 /* Multi-threaded row list render (rows[i] -> out + i*W*3): all host cores for
  * the CPU baseline. The reference loop has no mutable globals, so it is
  * re-entrant once the scene is read-only. */
@@ -136,7 +169,7 @@ typedef struct { void *h; int W, H; const int *rows; int n; uint8_t *out; int ti
 static void *ref_worker(void *a) {
   ref_job *j = (ref_job *)a;
   for (int i = j->tid; i < j->n; i += j->nthr)
-    ref_render_rows(j->h, j->W, j->H, j->rows[i], j->rows[i] + 1, j->out + (size_t)i * j->W * 3);
+    (ref_use_shoot ? ref_render_rows_shoot : ref_render_rows)(j->h, j->W, j->H, j->rows[i], j->rows[i] + 1, j->out + (size_t)i * j->W * 3);
   return NULL;
 }
 void ref_render_row_list(void *h, int W, int H, const int *rows, int n, uint8_t *out, int nthreads) {

@@ -248,6 +248,37 @@ static void trace(const rt_scene *sc, const float *o, const float *d, float *out
   for (int k = 0; k < 3; k++) out[k] = out[k] + c[k];
 }
 
+/* The dormant recursive tracer shoot() (C/raycast.c:152-296), orc_set_mode(1).  What it RETURNS: its refraction
+ * subtree (:186-243) is traced but the result is never added (the two lines that would are commented out, :293,295),
+ * so the value is the nested reflection sum
+ *     out_k = colour_k * opacity_k  +  out_(k+1) * reflectivity_k      (:291-294; out beyond the chain's end = black),
+ * with the same hits, shadow rays and Phong terms as the live iterative_shoot -- only the order of the float
+ * additions and multiplications differs (nested from the deepest hit outwards instead of a running product).
+ * recursion_level starts at MAX_LEVEL (7) and a call at level 0 returns black (:156-159): primary + 6 bounces, as
+ * the live path.  The discarded refraction rays are not traced here (dead code; in the reference they read
+ * uninitialised memory when the inner ray misses, :214-221). */
+static void trace_shoot(const rt_scene *sc, const float *o, const float *d, float *out, int level, int skip, orc_counters *ct) {
+  out[0] = out[1] = out[2] = 0;
+  if (level == 0) return;
+  float P[3], N[3];
+  if (ct) { if (skip < 0) ct->rays_primary++; else ct->rays_reflection++; }
+  const int hi = nearest(sc, o, d, P, N, skip, 0, ct);
+  if (hi < 0) return;
+  const rt_shape *ob = &sc->shapes[hi];
+  float rc[3] = {0, 0, 0};
+  if (ob->reflectivity > 0) {
+    float rv[3];
+    reflect3(rv, d, N);
+    norm3(rv);
+    if (level - 1 > 0) trace_shoot(sc, P, rv, rc, level - 1, hi, ct);
+  }
+  float c[3];
+  shade(sc, c, hi, P, N, d, ct);                        /* colour * opacity, :244-290 = calc_color */
+  for (int k = 0; k < 3; k++) out[k] = c[k] + rc[k] * ob->reflectivity;   /* :291-294 */
+}
+static int g_mode = 0;   /* 0: iterative_shoot (the live path), 1: shoot */
+void orc_set_mode(int m) { g_mode = m ? 1 : 0; }
+
 static inline float clampf(float v, float lo, float hi) { /* ppm_clamp, C/ppm.c:350-359 */
   if (v > hi) v = hi;
   if (v < lo) v = lo;
@@ -269,7 +300,8 @@ void orc_render_rows(const rt_scene *sc, int W, int H, int y0, int y1, uint8_t *
       d[1] = (float)(0 + ((double)sc->camera_height / 2.0) - (double)ph * (y + 0.5));
       d[2] = -1;
       norm3(d);
-      trace(sc, o, d, color, ct);
+      if (g_mode) trace_shoot(sc, o, d, color, MAX_LEVEL, -1, ct);
+      else trace(sc, o, d, color, ct);
       for (int k = 0; k < 3; k++) px[k] = quant(color[k] * 255);
       px += 3;
     }

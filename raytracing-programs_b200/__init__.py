@@ -43,7 +43,7 @@ class RtStats(C.Structure):
         ("flops", C.c_double), ("flops_shade", C.c_double), ("ms_kernels", C.c_double),
         ("ms_primary", C.c_double), ("ms_shade", C.c_double), ("ms_finalize", C.c_double),
         ("launches_shade", C.c_uint64), ("ms_gather", C.c_double), ("ms_total", C.c_double),
-        ("scan_slots", C.c_uint64)]
+        ("scan_slots", C.c_uint64), ("ball_tests_o", C.c_uint64), ("ball_tests_d", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -62,7 +62,7 @@ P3_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p)
 ABI_SYMBOLS = ("rt_init", "rt_init_device", "rt_device_count", "rt_shutdown", "rt_last_error",
                "rt_abi_version", "rt_scene_upload", "rt_render", "rt_render_device", "rt_render_rank",
                "rt_assemble_device", "rt_rank_rows_to_host", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows",
-               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel", "rt_set_max_depth",
+               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel", "rt_set_max_depth", "rt_set_mode",
                "rt_dbg_qindex_classify", "rt_dbg_qindex_prune", "rt_dbg_qindex_visit", "rt_dbg_qindex_last_nodes", "rt_dbg_light_buffer_sizes")
 
 _lib = None
@@ -145,6 +145,11 @@ class Renderer:
     def set_max_depth(self, depth):
         """MAX_RECURSION of C/raycast.c:14 (default 7); 50 = the bound of the reference's CUDA/OptiX variants."""
         _check(self.lib, self.lib.rt_set_max_depth(int(depth)), "rt_set_max_depth")
+
+    def set_mode(self, mode):
+        """0 = RT_MODE_ITERATIVE: iterative_shoot, the reference's live path (C/raycast.c:315-379); 1 = RT_MODE_SHOOT:
+        its dormant recursive shoot() (C/raycast.c:152-296).  Takes effect at the next render."""
+        _check(self.lib, self.lib.rt_set_mode(int(mode)), "rt_set_mode")
 
     def set_accel(self, mode):
         """0: every ray tests every shape (default). 1: light buffer for the sphere part of shadow queries

@@ -68,6 +68,7 @@ struct DeviceCtx {
   // per-tile working set
   size_t tile_cap = 0;
   float4 *acc = nullptr, *c0 = nullptr;
+  float4 *lvl = nullptr; size_t lvl_cap = 0;   // RT_MODE_SHOOT: per-level {colour, reflectivity} of a tile, [depth][tile_cap]
   float4 *qbuf = nullptr;     // 6 * tile_cap float4: two queues x {r0,r1,r2}
   int *qcount = nullptr;      // [RT_MAX_DEPTH_CAP + 1 levels][RT_CTL_STRIDE] queue control words (HitQueue::ctl)
   int *qcls = nullptr;        // 2 queues x RT_NCLS x tile_cap class lists
@@ -97,6 +98,7 @@ int prepare_kernels(DeviceCtx &d);   // launch plan of the resident scene (defin
 bool g_have_scene = false;
 int g_n_lights = 0, g_n_shapes = 0;
 int g_max_depth = 7;   // MAX_RECURSION, C/raycast.c:14; rt_set_max_depth
+int g_mode = 0;    // rt_set_mode: RT_MODE_ITERATIVE / RT_MODE_SHOOT
 int g_accel = 0;   // rt_set_accel / RT_ACCEL: light buffer for the sphere part of shadow queries
 
 // ---- NCCL through dlopen ---------------------------------------------------------
@@ -164,7 +166,7 @@ void free_device(DeviceCtx &d) {
   if (d.dev < 0) return;
   cudaSetDevice(d.dev);
   if (d.stream) cudaStreamSynchronize(d.stream);
-  cudaFree(d.scene_blob); cudaFree(d.acc); /* c0, qbuf, qcls live in the same block */ cudaFree(d.qcount);
+  cudaFree(d.scene_blob); cudaFree(d.lvl); cudaFree(d.acc); /* c0, qbuf, qcls live in the same block */ cudaFree(d.qcount);
   cudaFree(d.counters); cudaFree(d.rank_buf); cudaFree(d.staging); cudaFree(d.frame);
   cudaFree(d.p3_text); cudaFree(d.p3_state);
   for (int k = 0; k < 3; k++) { if (d.p3_pinned[k]) cudaFreeHost(d.p3_pinned[k]); if (d.p3_ev[k]) cudaEventDestroy(d.p3_ev[k]); }
@@ -612,6 +614,12 @@ long long rt_dbg_light_buffer_sizes(const rt_scene *scene, long long *per_level)
   return total;
 }
 
+int rt_set_mode(int mode) {
+  if (mode != RT_MODE_ITERATIVE && mode != RT_MODE_SHOOT) return set_err(RT_ERR_ARG, "rt_set_mode: mode must be RT_MODE_ITERATIVE or RT_MODE_SHOOT");
+  g_mode = mode;
+  return RT_OK;
+}
+
 int rt_set_accel(int mode) {
   if (mode != 0 && mode != 1) return set_err(RT_ERR_ARG, "rt_set_accel: mode must be 0 or 1");
   g_accel = mode;
@@ -880,6 +888,41 @@ int rt_scene_upload(const rt_scene *scene) {
     quad_idx.push_back(i);
   }
   for (int k = 0; k < 3; k++) quad_hot.push_back(make_float4(0.f, 0.f, 0.f, 0.f));   // prefetch spare
+  // Bounding balls for the pre-test of the quadric scan (rt_kernels.cuh, "Quadrics"; claim (1) of rt_qindex.cuh).  A certified
+  // ellipsoid cannot be reported for a line that passes its (float) centre farther than R = r_item (1 + 1e-4) + M reach,
+  // reach = |P - c| + r_item, M = the largest miss_rel of the scene (float slack of the test + rho).  With s = |P - c|:
+  // R = a + M s, a = r_item (1 + 1e-4 + M), and 2 a M s <= M (a^2 + s^2), so R^2 <= a^2 (1 + M) + s^2 M (1 + M).  The
+  // device test  max_j e_j^2 < T (1 - eps) - w (1 + eps)  with eps = M (1 + M) + 2^-16, w = a^2 (1 + M) / (1 - eps) (so that
+  // w (1 + eps) >= a^2 (1 + M) and then some) therefore proves dist(line, c)^2 = T - e^2 (up to the 2^-16 T of float slack
+  // for T, e and |d| != 1) > R^2.  Every other quadric gets w = +inf (kappa = -inf: always passes), pads -inf.
+  std::vector<float4> quad_ball;
+  float quad_ball_eps = 0.0f;
+  {
+    std::vector<QIndexItem> items(quad_order.size());
+    double M = 0.0;
+    const bool use_balls = !getenv("RT_NO_QBALL");
+    for (size_t k = 0; k < quad_order.size(); k++) {
+      items[k].ok = false;
+      if (use_balls) qindex_classify(scene->shapes[quad_order[k]].params, items[k]);
+      if (items[k].ok) M = std::max(M, (double)items[k].miss_rel);
+    }
+    const double eps = M * (1.0 + M) + 1.52587890625e-05;
+    quad_ball_eps = (float)eps;
+    if ((double)quad_ball_eps < eps) quad_ball_eps = nextafterf(quad_ball_eps, INFINITY);
+    for (size_t k = 0; k < quad_order.size(); k++) {
+      float4 e = make_float4(0.f, 0.f, 0.f, INFINITY);
+      if (items[k].ok && M < 0.05) {
+        const double a = (double)items[k].r_item * (1.0 + 1e-4 + M);
+        const double w = a * a * (1.0 + M) / (1.0 - (double)quad_ball_eps) * (1.0 + 1e-6);
+        float wf = (float)w;
+        if ((double)wf < w) wf = nextafterf(wf, INFINITY);
+        if (std::isfinite(wf)) e = make_float4(items[k].centre[0], items[k].centre[1], items[k].centre[2], wf);
+      }
+      quad_ball.push_back(e);
+    }
+    const size_t padded_q = (quad_ball.size() + 31) / 32 * 32 + 4;
+    while (quad_ball.size() < padded_q) quad_ball.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));
+  }
   // one blob, 256-byte aligned sections
   struct Sec { const void *src; size_t bytes; size_t off; };
   std::vector<float4> lb_hot;
@@ -887,7 +930,7 @@ int rt_scene_upload(const rt_scene *scene) {
   std::vector<float4> bvh_pair, qbvh_pair, qbvh_mpair;
   if (have_lb) bvh_child_pairs(bvh, bvh.node, bvh_pair);
   if (n_qidx) { bvh_child_pairs(qbvh, qbvh.node, qbvh_pair); bvh_child_pairs(qbvh, qbvh_marg, qbvh_mpair); }
-  Sec secs[32] = {
+  Sec secs[33] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
@@ -906,7 +949,8 @@ int rt_scene_upload(const rt_scene *scene) {
       {bvh_pair.data(), have_lb ? bvh_pair.size() * 16 : 0, 0}, {qbvh_pair.data(), n_qidx ? qbvh_pair.size() * 16 : 0, 0},
       {qbvh_mpair.data(), n_qidx ? qbvh_mpair.size() * 16 : 0, 0},
       {cam.start.data(), have_cam ? cam.start.size() * 4 : 0, 0}, {cam.items.data(), have_cam ? cam.items.size() * 4 : 0, 0},
-      {camq.start.data(), have_camq ? camq.start.size() * 4 : 0, 0}, {camq.items.data(), have_camq ? camq.items.size() * 4 : 0, 0}};
+      {camq.start.data(), have_camq ? camq.start.size() * 4 : 0, 0}, {camq.items.data(), have_camq ? camq.items.size() * 4 : 0, 0},
+      {quad_ball.data(), quad_ball.size() * 16, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -956,6 +1000,8 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.camq_items = have_camq ? (const int *)(b + secs[31].off) : nullptr;
     sc.n_qidx = n_qidx;
     sc.q_behind_rel = q_behind_rel;
+    sc.quad_ball = (const float4 *)(b + secs[32].off);
+    sc.quad_ball_eps = quad_ball_eps;
     sc.n_csph = getenv("RT_NO_CONST_SCAN") ? 0 : n_csph;   // debugging aid: force the global-operand loop
     sc.max_depth = g_max_depth;
     const int pr = prepare_kernels(d);
@@ -977,7 +1023,7 @@ int rt_scene_upload(const rt_scene *scene) {
 
 namespace {
 
-typedef void (*shade_fn_t)(DevScene, int, HitQueue, HitQueue, float4 *, float4 *, unsigned long long *);
+typedef void (*shade_fn_t)(DevScene, int, HitQueue, HitQueue, float4 *, float4 *, unsigned long long *, float4 *);
 
 // The k_shade instantiation for this scene: LB lights per pass, with / without the quadric sections,
 // with / without the light buffer.
@@ -1063,6 +1109,11 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     trace("enqueue_rank: tile working set allocated");
   }
   if (!d.shade) return set_err(RT_ERR_NO_SCENE, "render before rt_scene_upload");
+  const bool shoot = g_mode == RT_MODE_SHOOT;
+  if (shoot) {
+    const int rr = dev_realloc(d.lvl, d.lvl_cap, (size_t)g_max_depth * d.tile_cap * sizeof(float4));
+    if (rr != RT_OK) return rr;
+  }
   const int lb = d.lb;
   const shade_fn_t shade = (shade_fn_t)d.shade;
   HitQueue q[2];
@@ -1083,6 +1134,7 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     tg.first_px = first;
     tg.n_px = (int)((px_total - first) < (long long)tile ? (px_total - first) : (long long)tile);
     CK(cudaMemsetAsync(d.qcount, 0, (RT_MAX_DEPTH_CAP + 1) * RT_CTL_STRIDE * sizeof(int), d.stream));
+    if (shoot) CK(cudaMemsetAsync(d.lvl, 0, (size_t)g_max_depth * d.tile_cap * sizeof(float4), d.stream));   // no hit = black, reflectivity 0
     HitQueue q0 = q[0]; q0.ctl = d.qcount;
     const int ppx = d.sc.bvh_node ? 1 : RT_PRIM_PX_BRUTE;
     int gp = (tg.n_px + 256 * ppx - 1) / (256 * ppx); if (gp > d.grid_primary) gp = d.grid_primary;
@@ -1094,12 +1146,13 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
       HitQueue qin = q[level & 1], qout = q[(level + 1) & 1];
       qin.ctl = d.qcount + level * RT_CTL_STRIDE; qout.ctl = d.qcount + (level + 1) * RT_CTL_STRIDE;
       if ((mr = mark(d, 's')) != RT_OK) return mr;
-      shade<<<d.grid_shade, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters);
+      shade<<<d.grid_shade, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters,
+                                                shoot ? d.lvl + (size_t)level * d.tile_cap : nullptr);
       plan->launches++;
     }
     int gf = (tg.n_px / 4 + 256) / 256; if (gf > d.grid_fin) gf = d.grid_fin;
     if ((mr = mark(d, 'f')) != RT_OK) return mr;
-    k_finalize<<<gf, 256, 0, d.stream>>>(tg, d.acc, d.c0, dst);
+    k_finalize<<<gf, 256, 0, d.stream>>>(tg, d.acc, d.c0, dst, shoot ? d.lvl : nullptr, d.tile_cap, g_max_depth);
     plan->launches++;
     CK(cudaGetLastError());
   }
@@ -1130,8 +1183,9 @@ int collect_stats(int ndev, int W, int H, const RankPlan *plans, rt_stats *st, d
     s.quadric_tests_o += c[CT_QUAD_O]; s.quadric_tests_d += c[CT_QUAD_D];
     s.kernel_launches += plans[i].launches;
     s.scan_slots += c[CT_SLOTS];
+    s.ball_tests_o += c[CT_BALL_O]; s.ball_tests_d += c[CT_BALL_D];
     // SURVEY.md section 8a flop convention
-    const double all = 10.0 * c[CT_SPH_O] + 8.0 * c[CT_SPH_D] + 8.0 * c[CT_PLN_O] + 6.0 * c[CT_PLN_D] +
+    const double all = 10.0 * (c[CT_SPH_O] + c[CT_BALL_O]) + 8.0 * (c[CT_SPH_D] + c[CT_BALL_D]) + 8.0 * c[CT_PLN_O] + 6.0 * c[CT_PLN_D] +
                21.0 * c[CT_QUAD_O] + 37.0 * c[CT_QUAD_D] + 3.0 * c[CT_CANDIDATES] +
                77.0 * c[CT_LIGHT_SAMPLES] + 12.0 * c[CT_RAYS_SHADOW] + 21.0 * c[CT_RAYS_REFLECTION] +
                20.0 * c[CT_HIT_POINTS];

@@ -433,16 +433,16 @@ __device__ __noinline__ void resolve_spheres(const float (*dsm)[128], const int 
 // Survivors are recorded branch-free as bits (32 spheres per word, see resolve_spheres) and resolved after
 // the chunk, so the scan never diverges.  The arrays are padded to whole words with entries that never pass
 // (r^2 = -inf => kappa = +inf), plus one prefetch group.
+// scan_balls is the loop itself over any table of {centre, r^2} with margin eps: the spheres (eps = 2^-18), and the
+// bounding balls of the quadrics (DevScene::quad_ball), whose survivors go to resolve_quadrics.
 template <int NRV>
-RT_DEV void scan_chunk_g(const float (*dsm)[128], const int tid, const v3 P,
-                         const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
-                         unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
-  const float4 *hp = sc.sph_hot + cs;
+RT_DEV uint4 scan_balls(const float (*dsm)[128], const int tid, const v3 P, const float4 *__restrict__ table, const float eps,
+                        const int cs, const int nw) {
+  const float4 *hp = table + cs;
   v3 d[NRV];
   #pragma unroll
   for (int j = 0; j < NRV; j++) d[j] = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
   unsigned w0 = 0, w1 = 0, w2 = 0, w3 = 0;
-  const int nw = (n + 31) >> 5;
   float4 a0 = hp[0], a1 = hp[1];
   #pragma unroll 1
   for (int w = 0; w < nw; w++) {
@@ -456,8 +456,8 @@ RT_DEV void scan_chunk_g(const float (*dsm)[128], const int tid, const v3 P,
       const float x1 = P.x - g1.x, y1 = P.y - g1.y, z1 = P.z - g1.z;
       const float T0 = __fmaf_rn(z0, z0, __fmaf_rn(y0, y0, x0 * x0));
       const float T1 = __fmaf_rn(z1, z1, __fmaf_rn(y1, y1, x1 * x1));
-      const float ka0 = __fmaf_rn(-RT_FILTER_EPS, T0 + g0.w, T0 - g0.w);
-      const float ka1 = __fmaf_rn(-RT_FILTER_EPS, T1 + g1.w, T1 - g1.w);
+      const float ka0 = __fmaf_rn(-eps, T0 + g0.w, T0 - g0.w);
+      const float ka1 = __fmaf_rn(-eps, T1 + g1.w, T1 - g1.w);
       float mx0 = 0.0f, mx1 = 0.0f;
       #pragma unroll
       for (int j = 0; j < NRV; j++) {
@@ -469,7 +469,15 @@ RT_DEV void scan_chunk_g(const float (*dsm)[128], const int tid, const v3 P,
     }
     w3 = w2; w2 = w1; w1 = w0; w0 = ~wc;
   }
-  resolve_spheres(dsm, tid, P, sc, cs, nw, w0, w1, w2, w3, obj, r_on, alive, best_t, best_idx, n_cand);
+  return make_uint4(w0, w1, w2, w3);
+}
+template <int NRV>
+RT_DEV void scan_chunk_g(const float (*dsm)[128], const int tid, const v3 P,
+                         const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
+                         unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
+  const int nw = (n + 31) >> 5;
+  const uint4 w = scan_balls<NRV>(dsm, tid, P, sc.sph_hot, RT_FILTER_EPS, cs, nw);
+  resolve_spheres(dsm, tid, P, sc, cs, nw, w.x, w.y, w.z, w.w, obj, r_on, alive, best_t, best_idx, n_cand);
 }
 
 // The same scan with the sphere operands in the constant bank (rt_scene.cuh, c_sph): the production path.
@@ -544,21 +552,34 @@ RT_DEV void scan_chunk_c(const float (*dsm)[128], const int tid, const v3 P, con
   resolve_spheres(dsm, tid, P, sc, cs, nw, w0, w1, w2, w3, obj, r_on, alive, best_t, best_idx, n_cand);
 }
 
-// Resolve stage of the quadric scan, shared by all scan variants: filter recheck per ray still alive, then the
-// reference's expression tree (quadric_cq / quadric_t) and the z rule of C/raycast.c:492-494.
-__device__ __noinline__ void resolve_quadrics(const float (*dsm)[128], unsigned char (*cand)[128], const int tid, const v3 P,
-                                              const DevScene &sc, const int cs, const int nc, const int obj, const bool r_on,
-                                              unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
-  for (int i = 0; i < nc; i++) {
-    const int kk = cs + cand[i][tid];
+// Quadrics.  Every ray still meets every quadric, in two stages:
+//  (1) a conservative test against the quadric's BOUNDING BALL (DevScene::quad_ball, scan_balls): for an ellipsoid the
+//      host can certify (rt_qindex.cuh, qindex_classify: positive definite, well conditioned, real surface) a line that
+//      passes the centre farther than r_item + rho |P - c| has a negative discriminant IN THE REFERENCE'S FLOAT
+//      ARITHMETIC (claim (1) there), so the quadric cannot be reported for any ray of the hit point; every other
+//      quadric (cylinders, cones, paraboloids, flat or degenerate ones) has an infinite ball and always passes.
+//      Cost: the sphere filter's 8 + 3 per ray instead of the quadric filter's 45 + 14 per ray.
+//  (2) survivors, per thread: the FP32 quadric reject filter (rt_math.cuh) per ray still alive, then the reference's
+//      expression tree (quadric_cq / quadric_t, mixed float/double) and the z rule of C/raycast.c:492-494.
+__device__ __noinline__ void resolve_quadrics(const float (*dsm)[128], const int tid, const v3 P,
+                                              const DevScene &sc, const int cs, const int nw,
+                                              const unsigned w0, const unsigned w1, const unsigned w2, const unsigned w3,
+                                              const int obj, const bool r_on,
+                                              unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand, unsigned &n_setup, unsigned &n_filt) {
+  for (int k = nw - 1; k >= 0; k--)
+  for (unsigned sm = k == 0 ? w0 : k == 1 ? w1 : k == 2 ? w2 : w3; sm; sm &= ~(0x80000000u >> __clz(sm))) {
+    const int kk = cs + ((nw - 1 - k) << 5) + __clz(sm);
+    if (kk >= sc.n_quadrics) continue;
     const int idx = sc.quad_idx[kk];
     if (idx == obj) continue;                                  // C/raycast.c:450
     const QuadFilter f = quad_filter_setup(sc.quad_hot[3 * kk], sc.quad_hot[3 * kk + 1], sc.quad_hot[3 * kk + 2], P.x, P.y, P.z);
+    n_setup++;
     unsigned pm = 0;
     for (unsigned m = alive; m; m &= m - 1) {
       const int j = __ffs(m) - 1;
       const v3 dj = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
       pm |= (unsigned)(quad_filter_v(f, dj) >= 0.0f) << j;
+      n_filt++;
     }
     if (!pm) continue;
     const quad10 qq = load_quad(sc.quad, kk);
@@ -577,32 +598,13 @@ __device__ __noinline__ void resolve_quadrics(const float (*dsm)[128], unsigned 
   }
 }
 
-// Quadric scan of one chunk, same structure as scan_chunk: conservative FP32 reject filter
-// (rt_math.cuh, "quadric filter") for NRV rays in registers, survivors queued per thread and
-// resolved by the reference's expression tree (quadric_cq / quadric_t, mixed float/double)
-// plus the z rule of C/raycast.c:492-494.
 template <int NRV>
-RT_DEV void scan_quadrics(const float (*dsm)[128], unsigned char (*cand)[128], const int tid, const v3 P,
+RT_DEV void scan_quadrics(const float (*dsm)[128], const int tid, const v3 P,
                           const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
-                          unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
-  v3 d[NRV];
-  #pragma unroll
-  for (int j = 0; j < NRV; j++) d[j] = mk3(dsm[3 * j][tid], dsm[3 * j + 1][tid], dsm[3 * j + 2][tid]);
-  unsigned char *qp = &cand[0][tid];
-  const float4 *hp = sc.quad_hot + 3 * (size_t)cs;
-  float4 a0 = hp[0], a1 = hp[1], a2 = hp[2];
-  #pragma unroll 1
-  for (int k = 0; k < n; k++) {
-    hp += 3;
-    const QuadFilter f = quad_filter_setup(a0, a1, a2, P.x, P.y, P.z);
-    a0 = hp[0]; a1 = hp[1]; a2 = hp[2];                      // next quadric (one spare entry at the end)
-    float vmax = -1.0f;
-    #pragma unroll
-    for (int j = 0; j < NRV; j++) vmax = fmaxf(vmax, quad_filter_v(f, d[j]));
-    *qp = (unsigned char)k;
-    qp += (vmax >= 0.0f) ? 128 : 0;
-  }
-  resolve_quadrics(dsm, cand, tid, P, sc, cs, (int)(qp - &cand[0][tid]) >> 7, obj, r_on, alive, best_t, best_idx, n_cand);
+                          unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand, unsigned &n_setup, unsigned &n_filt) {
+  const int nw = (n + 31) >> 5;
+  const uint4 w = scan_balls<NRV>(dsm, tid, P, sc.quad_ball, sc.quad_ball_eps, cs, nw);
+  resolve_quadrics(dsm, tid, P, sc, cs, nw, w.x, w.y, w.z, w.w, obj, r_on, alive, best_t, best_idx, n_cand, n_setup, n_filt);
 }
 
 // One shadow ray (origin P, direction dj) against sphere slot ss: does the reference report a hit with
@@ -832,13 +834,13 @@ __device__ __noinline__ void scan_spheres_g(const int nrv, const float (*dsm)[12
   scan_chunk_g<NRV>(dsm, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
 }
 template <int NRV, int NRMIN>
-RT_DEV void scan_quadrics_v(const int nrv, const float (*dsm)[128], unsigned char (*cand)[128], const int tid, const v3 P,
+RT_DEV void scan_quadrics_v(const int nrv, const float (*dsm)[128], const int tid, const v3 P,
                             const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
-                            unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
+                            unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand, unsigned &n_setup, unsigned &n_filt) {
   if constexpr (NRV - RT_VSTEP >= NRMIN) {
-    if (nrv < NRV) { scan_quadrics_v<NRV - RT_VSTEP, NRMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand); return; }
+    if (nrv < NRV) { scan_quadrics_v<NRV - RT_VSTEP, NRMIN>(nrv, dsm, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand, n_setup, n_filt); return; }
   }
-  scan_quadrics<NRV>(dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+  scan_quadrics<NRV>(dsm, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand, n_setup, n_filt);
 }
 
 // QUADS = false: compiled without the quadric sections for scenes that have none (half the code:
@@ -848,17 +850,16 @@ RT_DEV void scan_quadrics_v(const int nrv, const float (*dsm)[128], unsigned cha
 template <int LB, bool QUADS, bool ACCEL>
 __global__ void __launch_bounds__(128, (ACCEL && !QUADS) ? 2 * RT_SHADE_MINB : RT_SHADE_MINB)   // no bundle scan: half the registers, twice the warps
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
-        float4 *__restrict__ c0, unsigned long long *__restrict__ counters) {
+        float4 *__restrict__ c0, unsigned long long *__restrict__ counters, float4 *__restrict__ lvl) {
   constexpr int NR = LB + 1;
   constexpr int VMIN = NR >= 3 ? NR - RT_VSTEP * ((NR - 3) / RT_VSTEP) : NR;   // smallest compiled variant
   auto pick_variant = [](int live) { const int v = NR - RT_VSTEP * ((NR - live) / RT_VSTEP); return v < VMIN ? VMIN : v; };
-  __shared__ unsigned char cand[QUADS ? RT_CHUNK + 1 : 1][128];   // survivor queue of the quadric scan (+1: its branch-free push stores before it knows)
   __shared__ float dsm[3 * NR][128];
   const int tid = threadIdx.x;
   // per-thread event counts (32-bit: a thread sees < 2^20 items per launch); the per-type test
   // counters are products of these with the scene's primitive counts, formed at the end
   unsigned n_refl = 0, n_lit = 0, n_hp = 0, n_pass_sum = 0, n_ls = 0, n_cand = 0;
-  unsigned d_sph = 0, d_pln = 0, d_quad = 0, d_slots = 0, o_sph = 0, o_quad = 0;   // direction tests executed: live ray slots x primitives scanned with them
+  unsigned d_sph = 0, d_pln = 0, d_quad = 0, d_slots = 0, o_sph = 0, o_quad = 0, d_ball = 0, o_ball = 0;   // direction tests executed: live ray slots x primitives scanned with them
   // Dynamic scheduling: every warp claims 32 consecutive entries of one class list at a time
   // (heaviest class first), so no SM idles while another still holds a backlog, and the hit
   // points a warp shades together need about the same number of ray slots.
@@ -1102,9 +1103,11 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
         }
         for (int cs = q0; cs < sc.n_quadrics; cs += RT_CHUNK) {
           const int n = min(RT_CHUNK, sc.n_quadrics - cs);
-          d_quad += (unsigned)__popc(alive) * (unsigned)n;
-          if (have) { d_slots += (unsigned)nrv * (unsigned)n; o_quad += (unsigned)n; }
-          scan_quadrics_v<NR, VMIN>(nrv, dsm, cand, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
+          // counted as executed: the bounding-ball tests (sphere-type tests: d_ball / o_ball) and, for the survivors, the
+          // quadric filter set-ups and per-ray evaluations (o_quad / d_quad, counted inside resolve_quadrics)
+          d_ball += (unsigned)__popc(alive) * (unsigned)n;
+          if (have) { d_slots += (unsigned)nrv * (unsigned)n; o_ball += (unsigned)n; }
+          scan_quadrics_v<NR, VMIN>(nrv, dsm, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand, o_quad, d_quad);
           if (nrv > VMIN) repack();
         }
       }
@@ -1150,6 +1153,10 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
     if (lit) out = mk3(mul32(out.x, opacity), mul32(out.y, opacity), mul32(out.z, opacity)); // :419
     if (!have) {
       // nothing to write for a stand-in lane
+    } else if (lvl != nullptr) {
+      // RT_MODE_SHOOT: colour and reflectivity of this hit, combined from the deepest level outwards by k_finalize
+      // (C/raycast.c:291-294); lvl = this level's slice of the per-tile buffer
+      lvl[pix] = make_float4(out.x, out.y, out.z, refl);
     } else if (level == 0) {
       c0[pix] = make_float4(out.x, out.y, out.z, 0.f);        // added last, C/raycast.c:377-378
     } else {
@@ -1169,9 +1176,9 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
                  make_float4(rd.x, rd.y, rd.z, mul32(tr, refl)), cls2);                  // total_refl, :345,362
     }
   }
-  unsigned v[12] = {n_refl, n_lit, n_hp, n_pass_sum, d_sph, n_ls, n_cand, d_pln, d_quad, d_slots, o_sph, o_quad};
+  unsigned v[14] = {n_refl, n_lit, n_hp, n_pass_sum, d_sph, n_ls, n_cand, d_pln, d_quad, d_slots, o_sph, o_quad, d_ball, o_ball};
   #pragma unroll
-  for (int k = 0; k < 12; k++) {
+  for (int k = 0; k < 14; k++) {
     #pragma unroll
     for (int off = 16; off; off >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
   }
@@ -1190,6 +1197,8 @@ k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict_
     if (v[10]) atomicAdd(&counters[CT_SPH_O], (u64)v[10]);
     if (v[5]) atomicAdd(&counters[CT_LIGHT_SAMPLES], (u64)v[5]);
     if (v[6]) atomicAdd(&counters[CT_CANDIDATES], (u64)v[6]);
+    if (v[12]) atomicAdd(&counters[CT_BALL_D], (u64)v[12]);
+    if (v[13]) atomicAdd(&counters[CT_BALL_O], (u64)v[13]);
   }
 }
 
@@ -1206,9 +1215,12 @@ RT_DEV unsigned quant8(float v) {
   return __float2uint_rz(v) & 0xffu;   // NaN -> 0
 }
 
+// RT_MODE_SHOOT (lvl != NULL): the pixel is the nested sum of shoot(), C/raycast.c:291-294,
+//   out_k = colour_k + out_(k+1) * reflectivity_k,  out beyond the last hit = black,
+// over the per-level records k_shade left in lvl[k * lvl_stride + pixel] (zero where the chain has no hit).
 __global__ void __launch_bounds__(256)
 k_finalize(TileGeom tg, const float4 *__restrict__ acc, const float4 *__restrict__ c0,
-           uint8_t *__restrict__ rank_buf) {
+           uint8_t *__restrict__ rank_buf, const float4 *__restrict__ lvl, size_t lvl_stride, int depth) {
   // groups are aligned on the rank buffer (pixel index multiple of 4 => byte offset multiple of 12)
   const long long g_first = tg.first_px >> 2, g_last = (tg.first_px + tg.n_px - 1) >> 2;
   const long long n_groups = g_last - g_first + 1;
@@ -1221,8 +1233,17 @@ k_finalize(TileGeom tg, const float4 *__restrict__ acc, const float4 *__restrict
     for (int k = 0; k < 4; k++) {
       long long i = px0 + k - tg.first_px;
       if (i >= 0 && i < tg.n_px) {
-        float4 a = acc[i], c = c0[i];
-        b[3 * k] = quant8(add32(a.x, c.x)); b[3 * k + 1] = quant8(add32(a.y, c.y)); b[3 * k + 2] = quant8(add32(a.z, c.z));
+        if (lvl != nullptr) {
+          float ox = 0.0f, oy = 0.0f, oz = 0.0f;
+          for (int l = depth - 1; l >= 0; l--) {
+            const float4 r = lvl[(size_t)l * lvl_stride + i];
+            ox = add32(r.x, mul32(ox, r.w)); oy = add32(r.y, mul32(oy, r.w)); oz = add32(r.z, mul32(oz, r.w));
+          }
+          b[3 * k] = quant8(ox); b[3 * k + 1] = quant8(oy); b[3 * k + 2] = quant8(oz);
+        } else {
+          float4 a = acc[i], c = c0[i];
+          b[3 * k] = quant8(add32(a.x, c.x)); b[3 * k + 1] = quant8(add32(a.y, c.y)); b[3 * k + 2] = quant8(add32(a.z, c.z));
+        }
       } else { full = false; b[3 * k] = b[3 * k + 1] = b[3 * k + 2] = 0; }
     }
     uint8_t *dst = rank_buf + px0 * 3;

@@ -22,6 +22,9 @@ struct DevScene {
   const int *pln_idx;
   const float4 *quad;       // [3*n_quadrics] {a,b,c,d} {e,f,g,h} {i,j,0,0}
   const float4 *quad_hot;   // [3*(n_quadrics+1)] reject-filter operands {A,B,C,D} {E,F,G,H} {I,J,S2,S1}
+  const float4 *quad_ball;  // [n_quadrics padded to 32 + 4] bounding ball {cx, cy, cz, w} of each quadric slot for the pre-test of the quadric
+                            // scan (rt_kernels.cuh, "Quadrics"): w = +inf for a quadric without a certified ball (always passes), -inf for pads
+  float quad_ball_eps;      // margin of that test: kappa = T (1 - eps) - w (1 + eps)
   const float4 *quad_prim;  // [3*n_quadrics] filter constants for the origin (0,0,0): {As,Bs,Cs,Ds} {Es,Fs,m0,eb} {gx,gy,gz,0}
   const int *quad_idx;
   const float4 *mat;        // [2*n_shapes] by original index: {Kd.rgb, reflectivity} {Ks.rgb, opacity}
@@ -123,5 +126,5 @@ struct HitQueue {
 enum {
   CT_RAYS_REFLECTION = 0, CT_RAYS_SHADOW, CT_HIT_POINTS, CT_PRIMARY_HITS,
   CT_SPH_O, CT_SPH_D, CT_PLN_O, CT_PLN_D, CT_QUAD_O, CT_QUAD_D,
-  CT_LIGHT_SAMPLES, CT_CANDIDATES, CT_SLOTS, CT_COUNT
+  CT_LIGHT_SAMPLES, CT_CANDIDATES, CT_SLOTS, CT_BALL_O, CT_BALL_D, CT_COUNT
 };

@@ -4,7 +4,7 @@
  * lists in file order, upload, render on the GPU(s), pixels land in photo_data.pixmap.
  * No CPU rendering path exists here: without a GPU the call fails loudly.
  * Environment knobs (the CLI stays 4 positional arguments): RT_GPUS (default 1,
- * 0 = all visible), RT_BAND_ROWS (band height of the multi-GPU row interleave).
+ * 0 = all visible), RT_BAND_ROWS (band height of the multi-GPU row interleave), RT_MAX_DEPTH, RT_MODE=shoot.
  */
 #include <string.h>
 #include "raycast_host.h"
@@ -87,6 +87,8 @@ void raycast(json_data_t *json_struct, PPMFormat photo_data) {
   }
   const char *md = getenv("RT_MAX_DEPTH");
   if (md && rt_set_max_depth(atoi(md)) != RT_OK) fail("bad RT_MAX_DEPTH");
+  const char *mode = getenv("RT_MODE");   /* "shoot": the reference's dormant recursive tracer, C/raycast.c:152-296 */
+  if (mode && rt_set_mode(strcmp(mode, "shoot") == 0 ? RT_MODE_SHOOT : RT_MODE_ITERATIVE) != RT_OK) fail("bad RT_MODE");
   if (rt_scene_upload(&scene) != RT_OK) fail("scene upload failed");
   if (rt_render(photo_data.width, photo_data.height, photo_data.pixmap, &g_last_stats) != RT_OK)
     fail("render failed");

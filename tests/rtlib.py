@@ -97,9 +97,11 @@ def ncores():
         return os.cpu_count() or 1
 
 
-def oracle_render(scene, W, H, rows=None, threads=None, counters=False, depth=7):
-    """Oracle image (all rows, or the given list of rows) as uint8 [n, W, 3]."""
+def oracle_render(scene, W, H, rows=None, threads=None, counters=False, depth=7, mode=0):
+    """Oracle image (all rows, or the given list of rows) as uint8 [n, W, 3].  mode=1: the reference's dormant
+    recursive shoot() (C/raycast.c:152-296) instead of the live iterative_shoot."""
     oracle().orc_set_max_level(int(depth))
+    oracle().orc_set_mode(int(mode))
     if isinstance(scene, (str, os.PathLike)):
         scene = pkg.load_scene(scene)
     rows = list(range(H)) if rows is None else list(rows)
@@ -109,11 +111,15 @@ def oracle_render(scene, W, H, rows=None, threads=None, counters=False, depth=7)
     oracle().orc_render_row_list(C.byref(scene), W, H, arr, len(rows), out.ctypes.data_as(C.c_void_p),
                                  threads or ncores(), C.byref(ct))
     oracle().orc_set_max_level(7)
+    oracle().orc_set_mode(0)
     return (out, ct) if counters else out
 
 
-def ref_render(scene_path, W, H, rows=None, threads=None, depth=7):
+def ref_render(scene_path, W, H, rows=None, threads=None, depth=7, mode=0):
+    """The patched reference itself.  mode=1: through its dormant recursive shoot() (oracle/ref_harness.c)."""
     r = ref(depth)
+    if mode:
+        r.ref_set_mode(1)
     h = r.ref_scene_load(os.fsencode(scene_path))
     if not h:
         raise RuntimeError(f"reference cannot open {scene_path}")
@@ -121,6 +127,8 @@ def ref_render(scene_path, W, H, rows=None, threads=None, depth=7):
     out = np.zeros((len(rows), W, 3), dtype=np.uint8)
     arr = (C.c_int * len(rows))(*rows)
     r.ref_render_row_list(h, W, H, arr, len(rows), out.ctypes.data_as(C.c_void_p), threads or ncores())
+    if mode:
+        r.ref_set_mode(0)
     r.ref_scene_free(h)
     return out
 
