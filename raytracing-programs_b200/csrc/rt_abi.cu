@@ -890,12 +890,12 @@ int rt_scene_upload(const rt_scene *scene) {
   for (int k = 0; k < 3; k++) quad_hot.push_back(make_float4(0.f, 0.f, 0.f, 0.f));   // prefetch spare
   // Bounding balls for the pre-test of the quadric scan (rt_kernels.cuh, "Quadrics"; claim (1) of rt_qindex.cuh).  A certified
   // ellipsoid cannot be reported for a line that passes its (float) centre farther than R = r_item (1 + 1e-4) + M reach,
-  // reach = |P - c| + r_item, M = the largest miss_rel of the scene (float slack of the test + rho).  With s = |P - c|:
-  // R = a + M s, a = r_item (1 + 1e-4 + M), and 2 a M s <= M (a^2 + s^2), so R^2 <= a^2 (1 + M) + s^2 M (1 + M).  The
-  // device test  max_j e_j^2 < T (1 - eps) - w (1 + eps)  with eps = M (1 + M) + 2^-16, w = a^2 (1 + M) / (1 - eps) (so that
-  // w (1 + eps) >= a^2 (1 + M) and then some) therefore proves dist(line, c)^2 = T - e^2 (up to the 2^-16 T of float slack
-  // for T, e and |d| != 1) > R^2.  Every other quadric gets w = +inf (kappa = -inf: always passes), pads -inf.
-  std::vector<float4> quad_ball;
+  // reach = |P - c| + r_item >= the distance to the exact centre, M = the largest miss_rel of the scene (float slack of the
+  // test + rho) -- the node test of the index, qnode_prune, with the node = the item.  With s = |P - c|: R = a + M s,
+  // a = r_item (1 + 1e-4 + M).  The device evaluates s from above (T rsqrt(T) (1 + 2^-20)) and rejects the quadric for every
+  // ray of the hit point when  max_j e_j^2 < T (1 - 2^-16) - R^2  (dist(line, c)^2 = T - e^2; 2^-16 T covers the roundings
+  // of T and e and |d| != 1, as the 1e-5 Tn of qnode_prune).  Every other quadric gets a = +inf (always passes), pads -inf.
+  std::vector<float4> quad_ball, quad_ball_prim;
   float quad_ball_eps = 0.0f;
   {
     std::vector<QIndexItem> items(quad_order.size());
@@ -906,19 +906,29 @@ int rt_scene_upload(const rt_scene *scene) {
       if (use_balls) qindex_classify(scene->shapes[quad_order[k]].params, items[k]);
       if (items[k].ok) M = std::max(M, (double)items[k].miss_rel);
     }
-    const double eps = M * (1.0 + M) + 1.52587890625e-05;
-    quad_ball_eps = (float)eps;
-    if ((double)quad_ball_eps < eps) quad_ball_eps = nextafterf(quad_ball_eps, INFINITY);
+    quad_ball_eps = (float)(M * (1.0 + 1e-6));
+    if ((double)quad_ball_eps < M) quad_ball_eps = nextafterf(quad_ball_eps, INFINITY);
     for (size_t k = 0; k < quad_order.size(); k++) {
       float4 e = make_float4(0.f, 0.f, 0.f, INFINITY);
-      if (items[k].ok && M < 0.05) {
-        const double a = (double)items[k].r_item * (1.0 + 1e-4 + M);
-        const double w = a * a * (1.0 + M) / (1.0 - (double)quad_ball_eps) * (1.0 + 1e-6);
-        float wf = (float)w;
-        if ((double)wf < w) wf = nextafterf(wf, INFINITY);
-        if (std::isfinite(wf)) e = make_float4(items[k].centre[0], items[k].centre[1], items[k].centre[2], wf);
+      if (items[k].ok) {
+        const double a = (double)items[k].r_item * (1.0 + 1e-4 + (double)quad_ball_eps) * (1.0 + 1e-6);
+        float af = (float)a;
+        if ((double)af < a) af = nextafterf(af, INFINITY);
+        if (std::isfinite(af)) e = make_float4(items[k].centre[0], items[k].centre[1], items[k].centre[2], af);
       }
       quad_ball.push_back(e);
+      // primary rays leave (0,0,0): T = |c|^2 and R are constants of the quadric; kappa = T (1 - 2^-16) - R^2 rounded
+      // down (a smaller kappa lets more through), stored negated; +inf = always passes
+      float4 ep = make_float4(0.f, 0.f, 0.f, INFINITY);
+      if (std::isfinite(e.w)) {
+        const double T = (double)e.x * e.x + (double)e.y * e.y + (double)e.z * e.z;
+        const double R = (double)e.w + (double)quad_ball_eps * sqrt(T) * (1.0 + 1e-6);
+        const double kap = T * (1.0 - 1.52587890625e-05) * (1.0 - 1e-6) - R * R * (1.0 + 1e-6);
+        float nk = (float)(-kap);
+        if ((double)nk < -kap) nk = nextafterf(nk, INFINITY);
+        if (std::isfinite(nk)) ep = make_float4(e.x, e.y, e.z, nk);
+      }
+      quad_ball_prim.push_back(ep);
     }
     const size_t padded_q = (quad_ball.size() + 31) / 32 * 32 + 4;
     while (quad_ball.size() < padded_q) quad_ball.push_back(make_float4(0.f, 0.f, 0.f, -INFINITY));
@@ -930,7 +940,7 @@ int rt_scene_upload(const rt_scene *scene) {
   std::vector<float4> bvh_pair, qbvh_pair, qbvh_mpair;
   if (have_lb) bvh_child_pairs(bvh, bvh.node, bvh_pair);
   if (n_qidx) { bvh_child_pairs(qbvh, qbvh.node, qbvh_pair); bvh_child_pairs(qbvh, qbvh_marg, qbvh_mpair); }
-  Sec secs[33] = {
+  Sec secs[34] = {
       {sph.data(), sph.size() * 16, 0},       {sph_prim.data(), sph_prim.size() * 16, 0},
       {sph_idx.data(), sph_idx.size() * 4, 0}, {pln.data(), pln.size() * 16, 0},
       {pln_idx.data(), pln_idx.size() * 4, 0}, {quad.data(), quad.size() * 16, 0},
@@ -950,7 +960,7 @@ int rt_scene_upload(const rt_scene *scene) {
       {qbvh_mpair.data(), n_qidx ? qbvh_mpair.size() * 16 : 0, 0},
       {cam.start.data(), have_cam ? cam.start.size() * 4 : 0, 0}, {cam.items.data(), have_cam ? cam.items.size() * 4 : 0, 0},
       {camq.start.data(), have_camq ? camq.start.size() * 4 : 0, 0}, {camq.items.data(), have_camq ? camq.items.size() * 4 : 0, 0},
-      {quad_ball.data(), quad_ball.size() * 16, 0}};
+      {quad_ball.data(), quad_ball.size() * 16, 0}, {quad_ball_prim.data(), quad_ball_prim.size() * 16, 0}};
   size_t total = 0;
   for (auto &s : secs) { s.off = total; total += (s.bytes + 255) & ~(size_t)255; }
   if (total == 0) total = 256;
@@ -1001,6 +1011,7 @@ int rt_scene_upload(const rt_scene *scene) {
     sc.n_qidx = n_qidx;
     sc.q_behind_rel = q_behind_rel;
     sc.quad_ball = (const float4 *)(b + secs[32].off);
+    sc.quad_ball_prim = (const float4 *)(b + secs[33].off);
     sc.quad_ball_eps = quad_ball_eps;
     sc.n_csph = getenv("RT_NO_CONST_SCAN") ? 0 : n_csph;   // debugging aid: force the global-operand loop
     sc.max_depth = g_max_depth;
@@ -1191,7 +1202,7 @@ int collect_stats(int ndev, int W, int H, const RankPlan *plans, rt_stats *st, d
                20.0 * c[CT_HIT_POINTS];
     // k_primary's share: per pixel every sphere (direction part only), plane and quadric once
     const double px = (double)plans[i].rows * W;
-    const double prim = px * (17.0 + 8.0 * d.sc.n_spheres + 14.0 * d.sc.n_planes + 58.0 * d.sc.n_quadrics) +
+    const double prim = px * (17.0 + 8.0 * d.sc.n_spheres + 14.0 * d.sc.n_planes + 8.0 * d.sc.n_quadrics) +   // (quadrics: their bounding-ball tests; the few that pass are left in k_shade's share)
                         20.0 * c[CT_PRIMARY_HITS];
     s.flops += all + px * 17.0 + 20.0 * c[CT_PRIMARY_HITS];
     s.flops_shade += all + px * 17.0 + 20.0 * c[CT_PRIMARY_HITS] - prim;

@@ -13,6 +13,9 @@
 #ifndef RT_SHADE_MINB
 #define RT_SHADE_MINB 4
 #endif
+#ifndef RT_SHADE_MINB_NARROW
+#define RT_SHADE_MINB_NARROW RT_SHADE_MINB   /* CTAs per SM of the instantiations with at most 8 lights per pass (9 ray slots) */
+#endif
 #ifndef RT_VSTEP
 #define RT_VSTEP 2       /* the bundle scans are compiled for NR, NR - RT_VSTEP, ... ray slots.  The instruction caches
                             decide (L0 ~6 KB per scheduler, L1.5 32 KB per SM): with 4-sphere trips and the resolve
@@ -163,7 +166,7 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
   const float pw = __fdiv_rn(sc.cam_w, (float)tg.width);    // C/raycast.c:110
   const float ph = __fdiv_rn(sc.cam_h, (float)tg.height);   // C/raycast.c:109
   const double half_w = __ddiv_rn((double)sc.cam_w, 2.0), half_h = __ddiv_rn((double)sc.cam_h, 2.0);
-  unsigned long long n_hits = 0, n_sph = 0, n_pln = 0, n_quad = 0, n_cand = 0;
+  unsigned long long n_hits = 0, n_sph = 0, n_pln = 0, n_quad = 0, n_cand = 0, n_ballsum = 0;
   const int stride = gridDim.x * blockDim.x * RT_PRIM_PX;
   const v3 o = mk3(0.0f, 0.0f, 0.0f);
   // block-uniform loop control (the per-thread offset is added inside): the warp stays provably converged, which the
@@ -299,7 +302,22 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
         }
       }
     }
+    unsigned long long n_ball = 0;
     for (int kq = kq0; kq < sc.n_quadrics; kq++) {
+      // bounding-ball pre-test (see "Quadrics" at k_shade): the origin is (0,0,0), so T = |c|^2, the radius and kappa are
+      // per-quadric constants prepared on the host: {cx, cy, cz, -kappa}; -kappa = +inf for a quadric without a ball
+      {
+        const float4 hb = sc.quad_ball_prim[kq];
+        float mb = -1.0f;
+        #pragma unroll
+        for (int k = 0; k < RT_PRIM_PX; k++) {
+          const float e = __fmaf_rn(d[k].z, hb.z, __fmaf_rn(d[k].y, hb.y, d[k].x * hb.x));
+          mb = fmaxf(mb, __fmaf_rn(e, e, hb.w));
+        }
+        n_ball += (unsigned)n_live;
+        if (!(mb >= 0.0f)) continue;
+      }
+      n_quad += (unsigned)n_live;
       const float4 p0 = sc.quad_prim[3 * kq], p1 = sc.quad_prim[3 * kq + 1], p2 = sc.quad_prim[3 * kq + 2];
       QuadFilter f;
       f.As = p0.x; f.Bs = p0.y; f.Cs = p0.z; f.Ds = p0.w; f.Es = p1.x; f.Fs = p1.y; f.m0 = p1.z; f.eb = p1.w;
@@ -322,7 +340,7 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
         }
       }
     }
-    n_quad += (unsigned long long)(sc.n_quadrics - kq0) * n_live;
+    n_ballsum += n_ball;
     #pragma unroll
     for (int k = 0; k < RT_PRIM_PX; k++) {
       const int i = base + k * blockDim.x;
@@ -350,8 +368,10 @@ k_primary(DevScene sc, TileGeom tg, float4 *__restrict__ acc, float4 *__restrict
     n_pln += __shfl_xor_sync(0xffffffffu, n_pln, off);
     n_quad += __shfl_xor_sync(0xffffffffu, n_quad, off);
     n_cand += __shfl_xor_sync(0xffffffffu, n_cand, off);
+    n_ballsum += __shfl_xor_sync(0xffffffffu, n_ballsum, off);
   }
   if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&counters[CT_BALL_D], n_ballsum);
     atomicAdd(&counters[CT_PRIMARY_HITS], n_hits);
     atomicAdd(&counters[CT_SPH_D], n_sph);
     atomicAdd(&counters[CT_PLN_D], n_pln);
@@ -435,7 +455,11 @@ __device__ __noinline__ void resolve_spheres(const float (*dsm)[128], const int 
 // (r^2 = -inf => kappa = +inf), plus one prefetch group.
 // scan_balls is the loop itself over any table of {centre, r^2} with margin eps: the spheres (eps = 2^-18), and the
 // bounding balls of the quadrics (DevScene::quad_ball), whose survivors go to resolve_quadrics.
-template <int NRV>
+// QB = false: table entries {centre, r^2}, kappa = (T - r^2) - eps (T + r^2) (the sphere filter).
+// QB = true: bounding balls of quadrics, entries {centre, a}: the ball's radius grows with the distance of the origin,
+// R = a + eps sqrt(T) (rt_abi.cu, "Bounding balls"), kappa = T (1 - 2^-16) - R |R|; a = +inf (no certified ball) gives
+// kappa = -inf (always passes), a = -inf (pads) +inf (never passes).  sqrt(T) = T rsqrt(T) rounded up by 2^-20.
+template <int NRV, bool QB>
 RT_DEV uint4 scan_balls(const float (*dsm)[128], const int tid, const v3 P, const float4 *__restrict__ table, const float eps,
                         const int cs, const int nw) {
   const float4 *hp = table + cs;
@@ -456,8 +480,15 @@ RT_DEV uint4 scan_balls(const float (*dsm)[128], const int tid, const v3 P, cons
       const float x1 = P.x - g1.x, y1 = P.y - g1.y, z1 = P.z - g1.z;
       const float T0 = __fmaf_rn(z0, z0, __fmaf_rn(y0, y0, x0 * x0));
       const float T1 = __fmaf_rn(z1, z1, __fmaf_rn(y1, y1, x1 * x1));
-      const float ka0 = __fmaf_rn(-eps, T0 + g0.w, T0 - g0.w);
-      const float ka1 = __fmaf_rn(-eps, T1 + g1.w, T1 - g1.w);
+      float ka0, ka1;
+      if constexpr (QB) {
+        const float R0 = __fmaf_rn(eps, T0 * rsqrtf(T0) * 1.000001f, g0.w), R1 = __fmaf_rn(eps, T1 * rsqrtf(T1) * 1.000001f, g1.w);
+        ka0 = __fmaf_rn(T0, 0.9999847412109375f, -(R0 * fabsf(R0)));
+        ka1 = __fmaf_rn(T1, 0.9999847412109375f, -(R1 * fabsf(R1)));
+      } else {
+        ka0 = __fmaf_rn(-eps, T0 + g0.w, T0 - g0.w);
+        ka1 = __fmaf_rn(-eps, T1 + g1.w, T1 - g1.w);
+      }
       float mx0 = 0.0f, mx1 = 0.0f;
       #pragma unroll
       for (int j = 0; j < NRV; j++) {
@@ -476,7 +507,7 @@ RT_DEV void scan_chunk_g(const float (*dsm)[128], const int tid, const v3 P,
                          const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
                          unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
   const int nw = (n + 31) >> 5;
-  const uint4 w = scan_balls<NRV>(dsm, tid, P, sc.sph_hot, RT_FILTER_EPS, cs, nw);
+  const uint4 w = scan_balls<NRV, false>(dsm, tid, P, sc.sph_hot, RT_FILTER_EPS, cs, nw);
   resolve_spheres(dsm, tid, P, sc, cs, nw, w.x, w.y, w.z, w.w, obj, r_on, alive, best_t, best_idx, n_cand);
 }
 
@@ -603,7 +634,7 @@ RT_DEV void scan_quadrics(const float (*dsm)[128], const int tid, const v3 P,
                           const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
                           unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand, unsigned &n_setup, unsigned &n_filt) {
   const int nw = (n + 31) >> 5;
-  const uint4 w = scan_balls<NRV>(dsm, tid, P, sc.quad_ball, sc.quad_ball_eps, cs, nw);
+  const uint4 w = scan_balls<NRV, true>(dsm, tid, P, sc.quad_ball, sc.quad_ball_eps, cs, nw);
   resolve_quadrics(dsm, tid, P, sc, cs, nw, w.x, w.y, w.z, w.w, obj, r_on, alive, best_t, best_idx, n_cand, n_setup, n_filt);
 }
 
@@ -848,7 +879,7 @@ RT_DEV void scan_quadrics_v(const int nrv, const float (*dsm)[128], const int ti
 // ACCEL = true: the sphere part of every shadow query goes through the light buffer (rt_scene.cuh)
 // instead of the bundle scan; the reflection ray still scans every sphere.
 template <int LB, bool QUADS, bool ACCEL>
-__global__ void __launch_bounds__(128, (ACCEL && !QUADS) ? 2 * RT_SHADE_MINB : RT_SHADE_MINB)   // no bundle scan: half the registers, twice the warps
+__global__ void __launch_bounds__(128, (ACCEL && !QUADS) ? 2 * RT_SHADE_MINB : (LB <= 8 ? RT_SHADE_MINB_NARROW : RT_SHADE_MINB))   // no bundle scan: half the registers, twice the warps
 k_shade(DevScene sc, int level, HitQueue qin, HitQueue qout, float4 *__restrict__ acc,
         float4 *__restrict__ c0, unsigned long long *__restrict__ counters, float4 *__restrict__ lvl) {
   constexpr int NR = LB + 1;

@@ -22,9 +22,11 @@ struct DevScene {
   const int *pln_idx;
   const float4 *quad;       // [3*n_quadrics] {a,b,c,d} {e,f,g,h} {i,j,0,0}
   const float4 *quad_hot;   // [3*(n_quadrics+1)] reject-filter operands {A,B,C,D} {E,F,G,H} {I,J,S2,S1}
-  const float4 *quad_ball;  // [n_quadrics padded to 32 + 4] bounding ball {cx, cy, cz, w} of each quadric slot for the pre-test of the quadric
-                            // scan (rt_kernels.cuh, "Quadrics"): w = +inf for a quadric without a certified ball (always passes), -inf for pads
-  float quad_ball_eps;      // margin of that test: kappa = T (1 - eps) - w (1 + eps)
+  const float4 *quad_ball;  // [n_quadrics padded to 32 + 4] bounding ball {cx, cy, cz, a} of each quadric slot for the pre-test of the quadric
+                            // scan (rt_kernels.cuh, "Quadrics"): radius a + quad_ball_eps |P - c|; a = +inf for a quadric without a
+                            // certified ball (always passes), -inf for pads (never pass)
+  const float4 *quad_ball_prim;   // [n_quadrics] the same test for the primary rays (origin exactly 0): {cx, cy, cz, -kappa}
+  float quad_ball_eps;      // M: the largest miss_rel among the certified ellipsoids (rt_qindex.cuh), rounded up
   const float4 *quad_prim;  // [3*n_quadrics] filter constants for the origin (0,0,0): {As,Bs,Cs,Ds} {Es,Fs,m0,eb} {gx,gy,gz,0}
   const int *quad_idx;
   const float4 *mat;        // [2*n_shapes] by original index: {Kd.rgb, reflectivity} {Ks.rgb, opacity}

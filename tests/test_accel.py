@@ -48,7 +48,7 @@ def test_accel_on_synthetic_scenes(renderer, scene, W, H):
     assert np.array_equal(a, b), rtlib.compare(a, b)
     assert sa.rays == sb.rays                                   # same rays of the reference semantics
     assert sb.sphere_tests_d < sa.sphere_tests_d                # fewer tests executed for them
-    assert sb.quadric_tests_d <= sa.quadric_tests_d
+    assert sb.quadric_tests_d <= sa.quadric_tests_d + sa.ball_tests_d
     assert np.array_equal(b, rtlib.oracle_render(scene, W, H))
 
 
@@ -121,7 +121,9 @@ def test_accel_quadric_index(renderer, tmp_path):
         b, sb = render(renderer, str(p), W, H, 1)
         assert np.array_equal(a, b), rtlib.compare(a, b)
         assert sa.rays == sb.rays
-        assert sb.quadric_tests_d * 3 < sa.quadric_tests_d          # the index does prune
+        # the index does prune: brute force meets every quadric with every ray (bounding-ball pre-tests + the quadric
+        # tests of those that pass them)
+        assert sb.quadric_tests_d * 3 < sa.quadric_tests_d + sa.ball_tests_d
         assert np.array_equal(b, rtlib.oracle_render(str(p), W, H))
     assert a.max() > 0 and len(np.unique(a)) > 50
 
@@ -182,7 +184,7 @@ def test_accel_scene_without_spheres(renderer, tmp_path):
         b, sb = render(renderer, str(p), 320, 240, 1)
         assert np.array_equal(a, b), rtlib.compare(a, b)
         assert sa.rays == sb.rays
-        assert sb.quadric_tests_d * 2 < sa.quadric_tests_d, (far, sb.quadric_tests_d, sa.quadric_tests_d)   # the mode is on
+        assert sb.quadric_tests_d * 2 < sa.quadric_tests_d + sa.ball_tests_d, (far, sb.quadric_tests_d, sa.quadric_tests_d, sa.ball_tests_d)   # the mode is on
         assert np.array_equal(b, rtlib.oracle_render(str(p), 320, 240))
         assert a.max() > 0
 
@@ -199,7 +201,7 @@ def test_accel_quadric_index_deep_bounces(renderer):
     finally:
         renderer.set_max_depth(7)
     assert np.array_equal(a, b), rtlib.compare(a, b)
-    assert sa.rays == sb.rays and sb.quadric_tests_d * 5 < sa.quadric_tests_d
+    assert sa.rays == sb.rays and sb.quadric_tests_d * 5 < sa.quadric_tests_d + sa.ball_tests_d
 
 
 @pytest.mark.timeout(900)

@@ -179,3 +179,48 @@ def test_zoo_scenes(renderer, name):
         rep = rtlib.compare(img, ora)
         assert rep["identical_frac"] == 1.0, (W, H, rep)
         assert int(st.rays_shadow) == ct.rays_shadow and int(st.rays_reflection) == ct.rays_reflection
+
+
+def _many_spheres_scene(path, n, seed=7):
+    """n small spheres (some mirrors) + a floor + 3 lights: more spheres than the constant bank of the scan holds."""
+    rng = np.random.RandomState(seed)
+    with open(path, "w") as f:
+        f.write("camera, width: 2.0, height: 1.5\n")
+        for i in range(n):
+            c = rng.uniform([-6, -1, -18], [6, 5, -4])
+            r = rng.uniform(0.05, 0.3)
+            refl = 0.5 if i % 7 == 0 else 0.0
+            f.write(f"sphere, radius: {r:.4f}, diffuse_color: [{rng.uniform(0.2, 1):.3f}, {rng.uniform(0.2, 1):.3f}, {rng.uniform(0.2, 1):.3f}], "
+                    f"specular_color: [0.5, 0.5, 0.5], position: [{c[0]:.4f}, {c[1]:.4f}, {c[2]:.4f}], reflectivity: {refl}, refractivity: 0, ior: 1\n")
+        f.write("plane, normal: [0, 1, 0], diffuse_color: [0.4, 0.4, 0.4], specular_color: [0, 0, 0], position: [0, -1.5, 0], reflectivity: 0.2, refractivity: 0, ior: 1\n")
+        for k in range(3):
+            f.write(f"light, color: [1, 1, 1], theta: 0, radial-a2: 0.01, radial-a1: 0.02, radial-a0: 1, position: [{-5 + 5 * k}, 8, {-2 - 3 * k}]\n")
+
+
+def test_more_spheres_than_the_constant_bank(renderer, tmp_path):
+    """3000 spheres: the first 2432 are scanned from the constant bank, the rest by the global-operand loop
+    (scan_spheres_g / the tail loop of k_primary); both against the oracle."""
+    path = str(tmp_path / "many.scene")
+    _many_spheres_scene(path, 3000)
+    renderer.upload(path)
+    img, st = renderer.raycast(96, 72)
+    ora = rtlib.oracle_render(path, 96, 72)
+    rep = rtlib.compare(img, ora)
+    print(rep, st.as_dict())
+    check(rep)
+    assert rep["identical_frac"] == 1.0
+
+
+def test_global_operand_scan_equals_constant_bank_scan(renderer):
+    """RT_NO_CONST_SCAN=1 (read at upload) sends every sphere through the global-operand loop: same bytes."""
+    renderer.upload(C4)
+    a, _ = renderer.raycast(128, 96)
+    os.environ["RT_NO_CONST_SCAN"] = "1"
+    try:
+        renderer.upload(C4)
+        b, _ = renderer.raycast(128, 96)
+    finally:
+        del os.environ["RT_NO_CONST_SCAN"]
+        renderer.upload(C4)
+    assert np.array_equal(a, b)
+    check(rtlib.compare(a, rtlib.oracle_render(C4, 128, 96)))
