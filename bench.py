@@ -641,6 +641,9 @@ def main():
             "launches": int(agg.launches_shade), "avg_launch_ms": shade_ms, "kernel_share_of_step": agg.ms_shade / max(agg.ms_kernels, 1e-9),
             "flops_per_launch": agg.flops_shade / max(agg.launches_shade, 1),
             "framebuffer_write_gbs": (W * H * 3 / world) / max(agg.ms_finalize, 1e-9) / 1e6, "hbm_peak_gbs": pk["hbm_gbs"]}
+    if os.environ.get("RT_ACCEL", "0") not in ("", "0"):
+        roof["note"] = ("RT_ACCEL=1: the exact index replaces the scans by list walks and hierarchy traversals; the kernel is "
+                        "latency-bound and this FP32 fraction does not describe it")
     if ncu_ref:
         roof["ncu_capture"] = ncu_ref        # pipe utilisation of the committed ncu capture (not measured in this run)
     if clocks and clocks.get("sm_mhz"):

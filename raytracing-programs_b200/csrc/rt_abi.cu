@@ -127,6 +127,15 @@ int nccl_load(int ndev) {
   SYM(GroupStart, "ncclGroupStart"); SYM(GroupEnd, "ncclGroupEnd");
   SYM(Send, "ncclSend"); SYM(Recv, "ncclRecv"); SYM(GetErrorString, "ncclGetErrorString");
 #undef SYM
+  // whatever libnccl.so.2 the process resolves (the one torch already mapped, else the system's): point-to-point
+  // send/recv inside a group needs 2.7+, and the structs of <nccl.h> we compile against are stable across 2.x
+  {
+    ncclResult_t (*get_version)(int *) = nullptr;
+    *(void **)(&get_version) = dlsym(g_nccl.lib, "ncclGetVersion");
+    int v = 0;
+    if (get_version && get_version(&v) == ncclSuccess && (v < 2700 || v >= 30000))
+      return set_err(RT_ERR_NCCL, "libnccl version %d is outside the supported range [2.7, 3.0)", v);
+  }
   int devs[RT_MAX_GPUS];
   for (int i = 0; i < ndev; i++) devs[i] = g_dev[i].dev;
   ncclResult_t r = g_nccl.CommInitAll(g_nccl.comms, ndev, devs);
@@ -1205,7 +1214,7 @@ int collect_stats(int ndev, int W, int H, const RankPlan *plans, rt_stats *st, d
     const double prim = px * (17.0 + 8.0 * d.sc.n_spheres + 14.0 * d.sc.n_planes + 8.0 * d.sc.n_quadrics) +   // (quadrics: their bounding-ball tests; the few that pass are left in k_shade's share)
                         20.0 * c[CT_PRIMARY_HITS];
     s.flops += all + px * 17.0 + 20.0 * c[CT_PRIMARY_HITS];
-    s.flops_shade += all + px * 17.0 + 20.0 * c[CT_PRIMARY_HITS] - prim;
+    s.flops_shade += std::max(0.0, all + px * 17.0 + 20.0 * c[CT_PRIMARY_HITS] - prim);   // (with the exact index on, k_primary's share is an over-estimate)
     if (i == 0) {
       for (size_t k = 0; k + 1 < d.evkind.size(); k++) {
         float t = 0;
