@@ -461,7 +461,8 @@ __device__ __noinline__ void resolve_spheres(const float (*dsm)[128], const int 
 // kappa = -inf (always passes), a = -inf (pads) +inf (never passes).  sqrt(T) = T rsqrt(T) rounded up by 2^-20.
 template <int NRV, bool QB>
 RT_DEV uint4 scan_balls(const float (*dsm)[128], const int tid, const v3 P, const float4 *__restrict__ table, const float eps,
-                        const int cs, const int nw) {
+                        const int cs, const int n) {
+  const int nw = (n + 31) >> 5;
   const float4 *hp = table + cs;
   v3 d[NRV];
   #pragma unroll
@@ -471,8 +472,9 @@ RT_DEV uint4 scan_balls(const float (*dsm)[128], const int tid, const v3 P, cons
   #pragma unroll 1
   for (int w = 0; w < nw; w++) {
     unsigned wc = 0;
+    const int cnt = (min(32, n - (w << 5)) + 1) & ~1;       // entries of this word, whole trips (a ragged last word: small scenes)
     #pragma unroll 1
-    for (int s = 0; s < 32; s += 2) {
+    for (int s = 0; s < cnt; s += 2) {
       hp += 2;
       const float4 g0 = a0, g1 = a1;
       a0 = hp[0]; a1 = hp[1];                                // next trip's operands (spare entries at the end)
@@ -498,7 +500,7 @@ RT_DEV uint4 scan_balls(const float (*dsm)[128], const int tid, const v3 P, cons
       wc = __funnelshift_l(__float_as_uint(__fmaf_rn(mx0, mx0, -ka0)), wc, 1);   // sign bit set = rejected (see scan_chunk_c)
       wc = __funnelshift_l(__float_as_uint(__fmaf_rn(mx1, mx1, -ka1)), wc, 1);
     }
-    w3 = w2; w2 = w1; w1 = w0; w0 = ~wc;
+    w3 = w2; w2 = w1; w1 = w0; w0 = (~wc) << (32 - cnt);     // first entry of the word in bit 31, entries never scanned = 0
   }
   return make_uint4(w0, w1, w2, w3);
 }
@@ -507,7 +509,7 @@ RT_DEV void scan_chunk_g(const float (*dsm)[128], const int tid, const v3 P,
                          const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
                          unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
   const int nw = (n + 31) >> 5;
-  const uint4 w = scan_balls<NRV, false>(dsm, tid, P, sc.sph_hot, RT_FILTER_EPS, cs, nw);
+  const uint4 w = scan_balls<NRV, false>(dsm, tid, P, sc.sph_hot, RT_FILTER_EPS, cs, n);
   resolve_spheres(dsm, tid, P, sc, cs, nw, w.x, w.y, w.z, w.w, obj, r_on, alive, best_t, best_idx, n_cand);
 }
 
@@ -554,8 +556,9 @@ RT_DEV void scan_chunk_c(const float (*dsm)[128], const int tid, const v3 P, con
   #pragma unroll 1
   for (int w = 0; w < nw; w++) {
     unsigned wc = 0;
+    const int cnt = (min(32, n - (w << 5)) + U - 1) & ~(U - 1);   // entries of this word, whole trips (a ragged last word: small scenes)
     #pragma unroll 1
-    for (int s = 0; s < 32; s += U) {
+    for (int s = 0; s < cnt; s += U) {
       float4 gc[U];
       #pragma unroll
 #if RT_PREFETCH2
@@ -578,7 +581,7 @@ RT_DEV void scan_chunk_c(const float (*dsm)[128], const int tid, const v3 P, con
         wc = __funnelshift_l(__float_as_uint(__fmaf_rn(m, m, -ka)), wc, 1);
       }
     }
-    w3 = w2; w2 = w1; w1 = w0; w0 = ~wc;
+    w3 = w2; w2 = w1; w1 = w0; w0 = (~wc) << (32 - cnt);       // first sphere of the word in bit 31, spheres never scanned = 0
   }
   resolve_spheres(dsm, tid, P, sc, cs, nw, w0, w1, w2, w3, obj, r_on, alive, best_t, best_idx, n_cand);
 }
@@ -634,7 +637,7 @@ RT_DEV void scan_quadrics(const float (*dsm)[128], const int tid, const v3 P,
                           const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
                           unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand, unsigned &n_setup, unsigned &n_filt) {
   const int nw = (n + 31) >> 5;
-  const uint4 w = scan_balls<NRV, true>(dsm, tid, P, sc.quad_ball, sc.quad_ball_eps, cs, nw);
+  const uint4 w = scan_balls<NRV, true>(dsm, tid, P, sc.quad_ball, sc.quad_ball_eps, cs, n);
   resolve_quadrics(dsm, tid, P, sc, cs, nw, w.x, w.y, w.z, w.w, obj, r_on, alive, best_t, best_idx, n_cand, n_setup, n_filt);
 }
 
