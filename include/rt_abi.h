@@ -143,6 +143,9 @@ int rt_set_mode(int mode);
  * same, byte for byte.  Env RT_ACCEL=0/1 overrides. */
 int rt_set_accel(int mode);
 
+/* ---- diagnostics, not part of the drop-in surface (INTEGRATION.md names the calls a binding needs) -------------
+ * Declared only with RT_ABI_DEBUG defined; the library always exports them (tests/test_qindex.py binds them by name). */
+#ifdef RT_ABI_DEBUG
 /* Diagnostics of the quadric index of the accelerated mode (csrc/rt_qindex.cuh); host arithmetic only, no GPU
  * needed.  tests/test_qindex.py drives them against the oracle's quadric intersector (C/raycast.c:614-656) to
  * check that the index can only drop quadrics the reference would not report.
@@ -170,6 +173,7 @@ int rt_dbg_qindex_visit(const float *q10, int n_quadrics, const float *P3, const
  * entries per (light, distance level), -1 for a level that is not built; returns the total, -1 if there is none. */
 long long rt_dbg_light_buffer_sizes(const rt_scene *scene, long long *per_level);
 long long rt_dbg_qindex_last_nodes(void);   /* hierarchy nodes tested by the last rt_dbg_qindex_visit call */
+#endif /* RT_ABI_DEBUG */
 
 /* Flatten to type-sorted SoA (+ original index) and upload to every device in use.
  * Takes the place of the list->VLA copy at C/raycast.c:87-107. The scene is copied;

@@ -17,6 +17,7 @@
 #include <utility>
 #include <vector>
 
+#define RT_ABI_DEBUG 1   /* the rt_dbg_* diagnostics are defined here */
 #include "rt_abi.h"
 #include "rt_kernels.cuh"
 #include "rt_p3.cuh"
