@@ -246,6 +246,35 @@ size_t rt_p3_max_bytes(int width, int height);
 int rt_p3_format_device(const void *dev_rgb, int width, int height, unsigned max_color,
                         void *dev_text, size_t text_cap, size_t *text_bytes, rt_p3_stats *stats);
 
+/* The same formatter for callers that must not allocate device memory.  (No counterpart in the reference: its
+ * writer is an fprintf loop on the host.  This entry point exists for the hosts this library gets embedded in.)
+ *
+ * Who needs it: a plug-in inside an application that has already handed the whole GPU to its own memory pool, where
+ * a cudaMalloc from a guest library either fails or eats into a budget the guest was never given; and a per-frame
+ * loop that cannot afford cudaMalloc / cudaFree, because both stall every stream of the device while they run.
+ * rt_p3_format_device keeps its span table (text length and start offset of every run of 65536 values) in a buffer
+ * it cudaMalloc's and grows on demand.  Here that table lives in a fixed array compiled into the library image
+ * instead (about 192 KiB; every GPU that loads the library carries it until the process exits), so the call itself
+ * makes no cudaMalloc, cudaFree, cudaHostAlloc or other allocating call.  rt_init is not required.
+ *
+ * dev_rgb (3*W*H bytes) and dev_text (capacity text_cap >= rt_p3_max_bytes(W, H)) are the caller's, both 16-byte
+ * aligned, on the device that is current in the calling thread; `stream` is a cudaStream_t of that device passed
+ * as a plain pointer (NULL = the default stream).  The kernels are queued on `stream`, then the call waits for
+ * that stream and stores the exact text length in *text_bytes (may be NULL).  The text is byte-identical to what
+ * rt_p3_format_device writes.
+ *
+ * Limits and rules:
+ *  - 3*W*H <= RT_P3_NOALLOC_MAX_VALUES (2^30 values, enough for a 16384 x 16384 frame); larger frames are refused
+ *    with RT_ERR_ARG and nothing is launched -- use rt_p3_format_device for those.
+ *  - The first call on each device looks up the table's device address and raises the formatter's shared-memory
+ *    limit on that device.  Make that first call during start-up, outside any stream capture.
+ *  - Every call on a device uses the same table and leaves its last contents in it (the call re-zeroes the part
+ *    it needs first).  Two calls that run on one GPU at the same time -- different streams or different host
+ *    threads -- corrupt each other's text; run them one after the other. */
+#define RT_P3_NOALLOC_MAX_VALUES (1ull << 30)
+int rt_p3_format_device_noalloc(const void *dev_rgb, int width, int height, unsigned max_color,
+                                void *dev_text, size_t text_cap, size_t *text_bytes, void *stream);
+
 /* Consumer of the text, called with consecutive pieces in order; non-zero aborts. */
 typedef int (*rt_p3_sink)(const void *data, size_t nbytes, void *user);
 

@@ -62,7 +62,7 @@ P3_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p)
 ABI_SYMBOLS = ("rt_init", "rt_init_device", "rt_device_count", "rt_shutdown", "rt_last_error",
                "rt_abi_version", "rt_scene_upload", "rt_render", "rt_render_device", "rt_render_rank",
                "rt_assemble_device", "rt_rank_rows_to_host", "rt_band_height", "rt_rank_num_rows", "rt_rank_rows",
-               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_write", "rt_set_accel", "rt_set_max_depth", "rt_set_mode",
+               "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_format_device_noalloc", "rt_p3_write", "rt_set_accel", "rt_set_max_depth", "rt_set_mode",
                "rt_dbg_qindex_classify", "rt_dbg_qindex_prune", "rt_dbg_qindex_visit", "rt_dbg_qindex_last_nodes", "rt_dbg_light_buffer_sizes")
 
 _lib = None
@@ -96,6 +96,8 @@ def load_library():
     lib.rt_p3_max_bytes.argtypes = [C.c_int, C.c_int]
     lib.rt_p3_format_device.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_size_t,
                                         C.POINTER(C.c_size_t), C.POINTER(RtP3Stats)]
+    lib.rt_p3_format_device_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_size_t,
+                                                C.POINTER(C.c_size_t), C.c_void_p]
     lib.rt_p3_write.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, P3_SINK, C.c_void_p, C.POINTER(RtP3Stats)]
     _lib = lib
     return lib
@@ -231,6 +233,23 @@ class Renderer:
 
     def close(self):
         self.lib.rt_shutdown()
+
+
+P3_NOALLOC_MAX_VALUES = 1 << 30     # RT_P3_NOALLOC_MAX_VALUES of include/rt_abi.h
+
+
+def p3_format_device_noalloc(rgb_ptr, width, height, text_ptr, text_cap, max_color=255, stream=None):
+    """rt_p3_format_device_noalloc: the P3 text of a device-resident RGB8 frame, written into the caller's device
+    buffer without any allocation inside the call.  For hosts whose GPU memory belongs to their own pool, or whose
+    frame loop cannot take the device-wide stall of cudaMalloc / cudaFree: the span table is a fixed array inside
+    the library, so frames are limited to P3_NOALLOC_MAX_VALUES bytes of pixmap.  Works on the current CUDA device and
+    needs no Renderer; `stream` is a raw cudaStream_t value (None = default stream).  One call at a time per GPU:
+    all calls share that table.  Returns the text length."""
+    lib = load_library()
+    n = C.c_size_t()
+    _check(lib, lib.rt_p3_format_device_noalloc(C.c_void_p(rgb_ptr), width, height, max_color, C.c_void_p(text_ptr),
+                                                text_cap, C.byref(n), C.c_void_p(stream)), "rt_p3_format_device_noalloc")
+    return n.value
 
 
 def rank_rows(height, rank, nranks):

@@ -1567,6 +1567,113 @@ int rt_p3_format_device(const void *dev_rgb, int W, int H, unsigned max_color, v
   return RT_OK;
 }
 
+}  // extern "C"
+
+// ---- P3 formatter for callers that may not allocate (rt_p3_format_device_noalloc) ---------------------------------
+// Same three kernels as p3_enqueue, but the span table is not a cudaMalloc'ed buffer: it is the array below, part of
+// the library image on every GPU that loads it ((16384 + 1) start offsets of 8 bytes + 16384 lengths of 4 = 196 616
+// bytes).  In host code `g_p3_na_table` is only a handle for the runtime, not a device address; the address a kernel
+// can use comes from cudaGetSymbolAddress, asked once per device with that device current (p3_na_device).
+#define P3_NA_MAX_SPANS ((unsigned)(RT_P3_NOALLOC_MAX_VALUES / P3_SPAN))
+static __device__ __align__(256) unsigned long long g_p3_na_table[(P3_NA_MAX_SPANS + 1) + P3_NA_MAX_SPANS / 2];
+
+namespace {
+
+struct P3Header { char b[64]; };
+
+// The file header travels as a kernel argument, so no host-to-device copy (and no staging buffer) is involved.
+__global__ void k_p3_header(P3Header h, int n, char *__restrict__ text) {
+  if ((int)threadIdx.x < n) text[threadIdx.x] = h.b[threadIdx.x];
+}
+
+#define P3_NA_MAX_DEVICES 64
+struct P3NaDevice {
+  bool ready = false;
+  unsigned long long *table = nullptr;   // device address of g_p3_na_table on this device
+  int sm_count = 0;
+} g_p3_na[P3_NA_MAX_DEVICES];
+
+// First call on a device (that device is current): architecture check, address of the table, shared-memory limit of
+// k_p3_emit.  Nothing here allocates on behalf of the caller; loading the kernels is the CUDA runtime's own business.
+int p3_na_device(int dev, P3NaDevice **out) {
+  if (dev < 0 || dev >= P3_NA_MAX_DEVICES) return set_err(RT_ERR_ARG, "rt_p3_format_device_noalloc: device ordinal %d not supported", dev);
+  P3NaDevice &s = g_p3_na[dev];
+  if (!s.ready) {
+    int major = 0, sms = 0;
+    CK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (major != 10)
+      return set_err(RT_ERR_NO_DEVICE, "rt_p3_format_device_noalloc: device %d is sm_%dx; the kernels are sm_100a only", dev, major);
+    void *p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_p3_na_table));
+    if (!p || ((uintptr_t)p & 255)) return set_err(RT_ERR_CUDA, "rt_p3_format_device_noalloc: bad address %p for the built-in span table", p);
+    CK(cudaFuncSetAttribute(k_p3_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, P3_SMEM_BYTES));
+    s.table = (unsigned long long *)p;
+    s.sm_count = sms;
+    s.ready = true;
+  }
+  *out = &s;
+  return RT_OK;
+}
+
+// dev_rgb / dev_text must be device (or managed) memory reachable from the current device: a host pointer, or memory
+// of another GPU, would otherwise only show up as a fault inside the kernels.
+int p3_na_check_pointer(const void *p, int dev, const char *name) {
+  cudaPointerAttributes pa;
+  const cudaError_t e = cudaPointerGetAttributes(&pa, p);
+  if (e != cudaSuccess) { cudaGetLastError(); return set_err(RT_ERR_ARG, "rt_p3_format_device_noalloc: %s is not a CUDA pointer (%s)", name, cudaGetErrorString(e)); }
+  if (pa.type == cudaMemoryTypeManaged) return RT_OK;
+  if (pa.type != cudaMemoryTypeDevice) return set_err(RT_ERR_ARG, "rt_p3_format_device_noalloc: %s is not device memory", name);
+  if (pa.device != dev) return set_err(RT_ERR_ARG, "rt_p3_format_device_noalloc: %s lives on device %d, the current device is %d", name, pa.device, dev);
+  return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_p3_format_device_noalloc(const void *dev_rgb, int W, int H, unsigned max_color, void *dev_text, size_t text_cap,
+                                size_t *text_bytes, void *stream_ptr) {
+  if (W <= 0 || H <= 0 || W > (1 << 26) || H > (1 << 26)) return set_err(RT_ERR_ARG, "bad image size %dx%d", W, H);
+  const unsigned long long n_values = (unsigned long long)W * (unsigned long long)H * 3ull;
+  if (n_values > RT_P3_NOALLOC_MAX_VALUES)
+    return set_err(RT_ERR_ARG, "rt_p3_format_device_noalloc: %dx%d has %llu values, the built-in span table ends at "
+                   "RT_P3_NOALLOC_MAX_VALUES = %llu; use rt_p3_format_device for this frame", W, H, n_values,
+                   (unsigned long long)RT_P3_NOALLOC_MAX_VALUES);
+  if (!dev_rgb || !dev_text || ((uintptr_t)dev_rgb & 15) || ((uintptr_t)dev_text & 15))
+    return set_err(RT_ERR_ARG, "rt_p3_format_device_noalloc: NULL or not 16-byte aligned device pointer");
+  if (text_cap < rt_p3_max_bytes(W, H)) return set_err(RT_ERR_ARG, "rt_p3_format_device_noalloc: text_cap below rt_p3_max_bytes");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { cudaGetLastError(); return set_err(RT_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e)); }
+  P3NaDevice *s = nullptr;
+  int r = p3_na_device(dev, &s);
+  if (r != RT_OK) return r;
+  if ((r = p3_na_check_pointer(dev_rgb, dev, "dev_rgb")) != RT_OK) return r;
+  if ((r = p3_na_check_pointer(dev_text, dev, "dev_text")) != RT_OK) return r;
+  cudaStream_t stream = (cudaStream_t)stream_ptr;
+  const unsigned long long n_chunks = (n_values + P3_CHUNK - 1) / P3_CHUNK;
+  const unsigned n_spans = (unsigned)((n_chunks + P3_SPAN_CHUNKS - 1) / P3_SPAN_CHUNKS);   // <= P3_NA_MAX_SPANS by the check above
+  unsigned long long *span_off = s->table;                                  // n_spans + 1 entries
+  unsigned *span_len = (unsigned *)(s->table + P3_NA_MAX_SPANS + 1);        // fixed place, whatever n_spans is
+  // the table still holds the previous call's lengths: k_p3_count adds into them, so they start at zero
+  CK(cudaMemsetAsync(span_len, 0, (size_t)n_spans * sizeof(unsigned), stream));
+  P3Header hdr;
+  memset(&hdr, 0, sizeof hdr);
+  const int hl = p3_header(hdr.b, sizeof hdr.b, W, H, max_color);
+  k_p3_header<<<1, 64, 0, stream>>>(hdr, hl, (char *)dev_text);
+  const unsigned long long gmax = 16ull * (unsigned long long)s->sm_count;
+  k_p3_count<<<(unsigned)(n_chunks < gmax ? n_chunks : gmax), P3_THREADS, 0, stream>>>((const uint8_t *)dev_rgb, n_values, n_chunks, span_len);
+  k_p3_scan<<<1, 1024, 0, stream>>>(span_len, span_off, n_spans, (unsigned long long)hl);
+  k_p3_emit<<<n_spans, P3_THREADS, P3_SMEM_BYTES, stream>>>((const uint8_t *)dev_rgb, n_values, n_chunks, span_off, n_spans, (char *)dev_text);
+  CK(cudaGetLastError());
+  unsigned long long total = 0;
+  CK(cudaMemcpyAsync(&total, span_off + n_spans, sizeof total, cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  if (text_bytes) *text_bytes = (size_t)total;
+  return RT_OK;
+}
+
 int rt_p3_write(const uint8_t *host_rgb, int W, int H, unsigned max_color, rt_p3_sink sink, void *user, rt_p3_stats *stats) {
   int r = p3_check(W, H);
   if (r != RT_OK) return r;
