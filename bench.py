@@ -109,6 +109,24 @@ def sample_rows(H, n):
     return sorted({int((i + 0.5) * H / n) for i in range(n)})
 
 
+def classify_divergent(gpu_img, cpu_img):
+    """Divergent pixels by kind, from the two images alone ({} when there are none).  hit_miss_flip: one side is the
+    background (no hit: 0,0,0; C/raycast.c:326) and the other is not; within_1_lsb: every channel within 1/255 (a
+    rounding neighbour, allowed by north_star); shadow_or_silhouette_flip: the rest (a light switched on or off by the
+    shadow epsilon, or another object won the nearest-hit search)."""
+    a = np.asarray(gpu_img, dtype=np.int16).reshape(-1, 3)
+    b = np.asarray(cpu_img, dtype=np.int16).reshape(-1, 3)
+    bad = (a != b).any(axis=1)
+    if not bad.any():
+        return {}
+    a, b = a[bad], b[bad]
+    miss = (a == 0).all(axis=1) != (b == 0).all(axis=1)
+    lsb = ~miss & (np.abs(a - b).max(axis=1) <= 1)
+    out = {"hit_miss_flip": int(miss.sum()), "within_1_lsb": int(lsb.sum()),
+           "shadow_or_silhouette_flip": int((~miss & ~lsb).sum())}
+    return {k: v for k, v in out.items() if v}
+
+
 def band_height():
     """RT_BAND_ROWS as the library reads it (csrc/rt_abi.cu band_rows); the reference arm must not load the product."""
     try:
@@ -393,7 +411,8 @@ def other_configs_leg(r, cpu=True):
             rep = rtlib.compare(host.numpy().reshape(h, w, 3), ref_img)
             ent["parity"] = {"against": "patched reference C path, full frame", "pixels": rep["pixels"],
                              "identical_frac": rep["identical_frac"], "max_abs_diff": rep["max_abs_diff"],
-                             "divergent_pixels": rep["pixels"] - rep["identical"]}
+                             "divergent_pixels": rep["pixels"] - rep["identical"],
+                             "divergent_classes": classify_divergent(host.numpy().reshape(h, w, 3), ref_img)}
             rows1 = sample_rows(h, max(1, min(h, int(h * 2.0 / max(t_all * cores, 1e-3)))))   # ~2 s of one thread
             t0 = time.perf_counter()
             rtlib.ref_render(sp, w, h, rows=rows1, threads=1)
@@ -428,6 +447,23 @@ def other_configs_leg(r, cpu=True):
                     a = np.array(open(asis_ppm, "rb").read().split(b"\n")[3:-1], dtype=np.int32).reshape(-1, 3)
                     b = np.array(open(ref_ppm, "rb").read().split(b"\n")[3:-1], dtype=np.int32).reshape(-1, 3)
                     cli["as_shipped_vs_patched_identical_frac"] = float((a == b).all(axis=1).mean())
+            refcuda_exe = os.path.join(ROOT, "oracle", "_ref", "raytrace_refcuda")
+            if os.path.exists(refcuda_exe):
+                # context only (north_star: "the repo's own CUDA/raycast.cu timed alongside"): unmodified CUDA/ sources
+                # rebuilt for sm_100a by oracle/build_ref.sh, cold process, its own timer lines; its image is NOT the
+                # reference's (its shadow and reflection logic differ from C/raycast.c), so it is no parity oracle
+                try:
+                    cu_ppm = os.path.join(tmp, key + "_refcuda.ppm")
+                    cwall, _, ctxt = run_cli(refcuda_exe, w, h, scn, cu_ppm)
+                    crun = None
+                    for line in ctxt.splitlines():
+                        if line.startswith("Time (sec) to run the ray tracer"):
+                            crun = float(line.rsplit(":", 1)[1])
+                    cli["reference_cuda_variant"] = {"run_the_ray_tracer_s": crun, "process_wall_s": cwall,
+                                                     "ours_render_s": render_s, "ours_kernels_ms": m,
+                                                     "note": "CUDA/raycast.cu as shipped, sm_100a rebuild; context, not parity"}
+                except Exception as e:
+                    cli["reference_cuda_variant"] = {"error": str(e)[:160]}
             ent["cli"] = cli
         except Exception as e:                                       # the CLI leg must not take the headline down
             ent["cli"] = {"error": str(e)[:200]}
@@ -459,7 +495,21 @@ def library_multi_gpu_selftest(r, world, local_rank):
             rn.raycast_into(w, h, pinned.data_ptr())                     # pinned pixmap: every GPU copies its own bands
             res["direct_copy_path_equal"] = bool(np.array_equal(one.reshape(-1), pinned.numpy()))
             res["frame"] = f"{nm.split(':')[0]} scene at {w}x{h}"
-            res["ms_gather"] = st.ms_gather
+            res["ms_gather_first_call"] = st.ms_gather                  # includes NCCL's first-use channel set-up
+            # steady state of the path the drop-in CLI takes with RT_GPUS=N: C4 at its named size, frame left on GPU 0
+            # (rt_render_device: per-GPU bands, ncclSend/ncclRecv gather, k_assemble), after two warm-up frames
+            nm4, sp4, w4, h4 = WORKLOADS["c4"]
+            rn.upload(sp4)
+            for _ in range(2):
+                rn.raycast_device(w4, h4)
+            fr = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                _, s4 = rn.raycast_device(w4, h4)
+                fr.append({"ms_total": (time.perf_counter() - t0) * 1e3, "ms_kernels": s4.ms_kernels, "ms_gather": s4.ms_gather})
+            best = min(fr, key=lambda f: f["ms_total"])
+            res["steady_state_c4"] = dict(best, frames=3, mrays_per_s=s4.rays / best["ms_total"] / 1e3,
+                                          note="one process drives all GPUs; host clock around rt_render_device")
         finally:
             rn.close()
         r.__init__(device=local_rank)
@@ -529,34 +579,45 @@ def main():
         dist.barrier()
         host_np = np.memmap(shm_path, dtype=np.uint8, mode="r+", shape=(W * H * 3,))
         host_frame = torch.from_numpy(host_np)
+        # Every rank holds its mapping now, so the NAME can go at once: the pages live until the last rank unmaps them
+        # (process exit at the latest), and nothing is left behind in /dev/shm whatever happens further down.
+        dist.barrier()
+        if rank == 0:
+            os.unlink(shm_path)
         rc = torch.cuda.cudart().cudaHostRegister(host_frame.data_ptr(), W * H * 3, 0)
         if int(rc) != 0:
             raise RuntimeError(f"cudaHostRegister of the shared host frame failed: {rc}")
+
+    def release_host_frame():
+        """Drop the page lock of the shared pixmap (N > 1) before the rank leaves."""
+        if shm_path is not None:
+            torch.cuda.synchronize()
+            torch.cuda.cudart().cudaHostUnregister(host_frame.data_ptr())
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def gather_to_rank0():
-        """Band gather: every rank's rows to rank 0 over NCCL (NVLink), then de-interleave."""
+    def render_resident(Wx, Hx, rb, stg, frm, szs, ofs):
+        """One Wx x Hx frame, scene resident, frame left on rank 0's GPU; returns (device ms, stats).  N > 1: every rank's
+        rows go to rank 0 over NCCL (NVLink) and are de-interleaved there; that time is part of the figure."""
+        if world == 1:
+            _, _, st = r.raycast_rank(Wx, Hx, 0, 1, frm.data_ptr())
+            return st.ms_kernels, st
+        _, _, st = r.raycast_rank(Wx, Hx, rank, world, rb.data_ptr())
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        bands.gather_to_rank0(rank_buf, staging, sizes, offs, rank, world)
+        bands.gather_to_rank0(rb, stg, szs, ofs, rank, world)
         torch.cuda.current_stream().synchronize()      # k_assemble runs on the library's own stream
         if rank == 0:
-            r.assemble(W, H, world, staging.data_ptr(), offs, frame.data_ptr())
+            r.assemble(Wx, Hx, world, stg.data_ptr(), ofs, frm.data_ptr())
         e1.record()
         torch.cuda.synchronize()
-        return e0.elapsed_time(e1)
+        return st.ms_kernels + e0.elapsed_time(e1), st
 
     def step_resident():
-        """One frame, scene resident; returns (device ms, stats)."""
-        if world == 1:
-            _, _, st = r.raycast_rank(W, H, 0, 1, frame.data_ptr())
-            return st.ms_kernels, st
-        _, _, st = r.raycast_rank(W, H, rank, world, rank_buf.data_ptr())
-        return st.ms_kernels + gather_to_rank0(), st
+        return render_resident(W, H, rank_buf, staging, frame, sizes, offs)
 
     def step_e2e():
         """The public call: flatten + upload the scene, render, pixmap in host memory (N = 1: rt_render into pinned
@@ -615,9 +676,45 @@ def main():
     barrier()
     e2e_ms = allmax((time.perf_counter() - t0) * 1e3 / args.steps)
     e2e = {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "ms_per_step": e2e_ms,
-           "h2d_bytes_per_step": scene_bytes(sc) * world, "d2h_bytes_per_step": W * H * 3}
+           "h2d_bytes_per_step": scene_bytes(sc) * world, "d2h_bytes_per_step": W * H * 3,
+           "path": ("rt_scene_upload + rt_render into a pinned host pixmap" if world == 1 else
+                    "per rank: rt_scene_upload + rt_render_rank + rt_rank_rows_to_host, i.e. every GPU copies its own bands over "
+                    "its own PCIe link into one page-locked pixmap in POSIX shared memory (no gather to rank 0 on this path; "
+                    "the device-timed value above does include the NCCL gather)")}
+
+    # ---- BASELINE config 5 at its named size: one timed frame at this N (every rank takes part) -------------
+    c5 = None
+    if args.workload == "c4" and not args.size and not args.no_extra and os.environ.get("RT_BENCH_C5", "1") != "0":
+        nm5, sp5, w5, h5 = WORKLOADS["c5"]
+        sc5 = pkg.load_scene(sp5)
+        r.upload(sc5)
+        szs5, ofs5 = bands.layout(w5, h5, world)
+        rb5 = torch.empty(szs5[rank] + 256, dtype=torch.uint8, device=dev)
+        frm5 = stg5 = None
+        if rank == 0:
+            frm5 = torch.empty(w5 * h5 * 3, dtype=torch.uint8, device=dev)
+            if world > 1:
+                stg5 = torch.empty(ofs5[-1] + szs5[-1] + 256, dtype=torch.uint8, device=dev)
+        for _ in range(2):                               # warm-up at 1/64 of the frame: loads this scene's k_shade variant
+            r.raycast_rank(w5 // 8, h5 // 8, rank, world, rb5.data_ptr())
+        flush.fill_(1)
+        barrier()
+        ms5, st5 = render_resident(w5, h5, rb5, stg5, frm5, szs5, ofs5)
+        barrier()
+        r5p, r5r, r5s, fl5 = allsum([st5.rays_primary, st5.rays_reflection, st5.rays_shadow, st5.flops])
+        ms5 = allmax(ms5)
+        c5 = {"workload": nm5, "metric": "Mrays/s (primary+secondary)", "value": (r5p + r5r + r5s) / ms5 / 1e3, "unit": "Mrays/s",
+              "n_gpus": world, "steps": 1, "warmup": f"2 frames at {w5 // 8}x{h5 // 8}", "ms_per_step": ms5, "scaling": "strong",
+              "mpixels_per_s": w5 * h5 / ms5 / 1e3, "frac_fp32_peak": fl5 / ms5 / 1e9 / (pk["fp32_tflops"] * world),
+              "k_shade_frac_fp32_peak_rank0": st5.flops_shade / max(st5.ms_shade, 1e-9) / 1e9 / pk["fp32_tflops"],
+              "mode": "brute force (RT_ACCEL=0): every ray tests all 4096 shapes",
+              "timing": "device time (CUDA events on the launching streams) + NCCL gather and de-interleave, max over ranks; "
+                        "L2 flushed before the frame; parity of this configuration: tests/test_named_sizes.py"}
+        del rb5, frm5, stg5
+        r.upload(sc)
 
     if rank != 0:
+        release_host_frame()
         r.close()
         if world > 1:
             dist.destroy_process_group()
@@ -702,8 +799,11 @@ def main():
                                                            "(the reference as shipped is single-threaded)"}}
         out["parity"] = {"against": "patched reference C path" if kind == "reference" else "oracle port", "rows": len(rows),
                          "pixels": rep["pixels"], "identical_frac": rep["identical_frac"], "max_abs_diff": rep["max_abs_diff"],
-                         "divergent_pixels": rep["pixels"] - rep["identical"]}
+                         "divergent_pixels": rep["pixels"] - rep["identical"],
+                         "divergent_classes": classify_divergent(gpu_img, cpu_img)}
 
+    if c5 is not None:
+        out["c5"] = c5
     # ---- P3 writer: HBM-bound formatter on the same frame -------
     if world == 1 and not args.no_extra:
         out["p3_writer"] = p3_leg(r, W, H, frame, flush, pk, host_frame, cpu=not args.no_cpu)
@@ -721,6 +821,7 @@ def main():
     if world > 1 and not args.no_extra:
         out["library_multi_gpu_selftest"] = library_multi_gpu_selftest(r, world, local_rank)
     print(json.dumps(out))
+    release_host_frame()
     r.close()
     if world > 1:
         dist.destroy_process_group()
