@@ -24,7 +24,12 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+/* Version of this header, returned by rt_abi_version() of the library that was loaded: a binding compares the two
+ * before it passes any struct.  History: 1 = round-1 surface; 2 = rt_stats grew by scan_slots, ball_tests_o,
+ * ball_tests_d (structs only ever grow at the end, and only together with a version bump: a caller built against an
+ * older header would hand the library a buffer that is too short), new calls rt_set_mode, rt_rank_rows_to_host,
+ * rt_p3_format_device_noalloc. */
+#define RT_ABI_VERSION 2
 
 typedef enum rt_status {
   RT_OK = 0,

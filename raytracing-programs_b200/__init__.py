@@ -65,6 +65,8 @@ ABI_SYMBOLS = ("rt_init", "rt_init_device", "rt_device_count", "rt_shutdown", "r
                "rt_p3_max_bytes", "rt_p3_format_device", "rt_p3_format_device_noalloc", "rt_p3_write", "rt_set_accel", "rt_set_max_depth", "rt_set_mode",
                "rt_dbg_qindex_classify", "rt_dbg_qindex_prune", "rt_dbg_qindex_visit", "rt_dbg_qindex_last_nodes", "rt_dbg_light_buffer_sizes")
 
+ABI_VERSION = 2     # RT_ABI_VERSION of include/rt_abi.h the structs above mirror
+
 _lib = None
 _host = None
 
@@ -80,6 +82,8 @@ def load_library():
                       "there is no fallback renderer")
     lib = C.CDLL(path, mode=C.RTLD_GLOBAL)
     lib.rt_last_error.restype = C.c_char_p
+    if lib.rt_abi_version() != ABI_VERSION:     # the ctypes mirrors below are laid out for exactly this header version
+        raise RtError(f"{path} speaks ABI version {lib.rt_abi_version()}, this binding was written for {ABI_VERSION}: rebuild")
     lib.rt_scene_upload.argtypes = [C.POINTER(RtScene)]
     lib.rt_render.argtypes = [C.c_int, C.c_int, C.c_void_p, C.POINTER(RtStats)]
     lib.rt_render_device.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(RtStats)]

@@ -69,7 +69,7 @@ struct DeviceCtx {
   // per-tile working set
   size_t tile_cap = 0;
   float4 *acc = nullptr, *c0 = nullptr;
-  float4 *lvl = nullptr; size_t lvl_cap = 0;   // RT_MODE_SHOOT: per-level {colour, reflectivity} of a tile, [depth][tile_cap]
+  float4 *lvl = nullptr; size_t lvl_cap = 0;   // RT_MODE_SHOOT: per-level {colour, reflectivity} of a tile, [depth][tile of the render]
   float4 *qbuf = nullptr;     // 6 * tile_cap float4: two queues x {r0,r1,r2}
   int *qcount = nullptr;      // [RT_MAX_DEPTH_CAP + 1 levels][RT_CTL_STRIDE] queue control words (HitQueue::ctl)
   int *qcls = nullptr;        // 2 queues x RT_NCLS x tile_cap class lists
@@ -1114,6 +1114,13 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
   plan->rows = rows; plan->bytes = (size_t)px_total * 3; plan->launches = 0;
   size_t tile = tile_pixels_cap();
   if ((long long)tile > px_total) tile = (size_t)(px_total > 0 ? px_total : 1);
+  const bool shoot = g_mode == RT_MODE_SHOOT;
+  if (shoot) {
+    // RT_MODE_SHOOT keeps one {colour, reflectivity} record per level and pixel of a tile: bound that buffer to 2 GiB
+    // whatever the depth (rt_set_max_depth(50) with the default 16 M pixel tile would ask for 13 GB) by shrinking the tile
+    const size_t cap = (((size_t)2 << 30) / (sizeof(float4) * (size_t)g_max_depth)) & ~(size_t)1023;
+    if (tile > cap) tile = cap;
+  }
   if (tile > d.tile_cap || !d.acc) {
     // one allocation for the whole per-tile working set (acc, c0, two queues, class lists)
     CK(cudaStreamSynchronize(d.stream));
@@ -1130,10 +1137,12 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     trace("enqueue_rank: tile working set allocated");
   }
   if (!d.shade) return set_err(RT_ERR_NO_SCENE, "render before rt_scene_upload");
-  const bool shoot = g_mode == RT_MODE_SHOOT;
+  const size_t lvl_stride = tile;   // pixels per level slice of d.lvl (this render's tile, not the allocated capacity)
   if (shoot) {
-    const int rr = dev_realloc(d.lvl, d.lvl_cap, (size_t)g_max_depth * d.tile_cap * sizeof(float4));
-    if (rr != RT_OK) return rr;
+    const size_t need = (size_t)g_max_depth * lvl_stride * sizeof(float4);
+    if (dev_realloc(d.lvl, d.lvl_cap, need) != RT_OK)
+      return set_err(RT_ERR_OOM, "RT_MODE_SHOOT: cannot allocate the per-level buffer (%zu MiB = depth %d x %zu pixels x 16 B); "
+                     "lower RT_TILE_PIXELS or the depth", need >> 20, g_max_depth, lvl_stride);
   }
   const int lb = d.lb;
   const shade_fn_t shade = (shade_fn_t)d.shade;
@@ -1155,7 +1164,9 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
     tg.first_px = first;
     tg.n_px = (int)((px_total - first) < (long long)tile ? (px_total - first) : (long long)tile);
     CK(cudaMemsetAsync(d.qcount, 0, (RT_MAX_DEPTH_CAP + 1) * RT_CTL_STRIDE * sizeof(int), d.stream));
-    if (shoot) CK(cudaMemsetAsync(d.lvl, 0, (size_t)g_max_depth * d.tile_cap * sizeof(float4), d.stream));   // no hit = black, reflectivity 0
+    if (shoot)                                                     // no hit = black, reflectivity 0: only the pixels of this tile
+      for (int level = 0; level < g_max_depth; level++)
+        CK(cudaMemsetAsync(d.lvl + (size_t)level * lvl_stride, 0, (size_t)tg.n_px * sizeof(float4), d.stream));
     HitQueue q0 = q[0]; q0.ctl = d.qcount;
     const int ppx = d.sc.bvh_node ? 1 : RT_PRIM_PX_BRUTE;
     int gp = (tg.n_px + 256 * ppx - 1) / (256 * ppx); if (gp > d.grid_primary) gp = d.grid_primary;
@@ -1168,12 +1179,12 @@ int enqueue_rank(DeviceCtx &d, int W, int H, int rank, int nranks, uint8_t *dst,
       qin.ctl = d.qcount + level * RT_CTL_STRIDE; qout.ctl = d.qcount + (level + 1) * RT_CTL_STRIDE;
       if ((mr = mark(d, 's')) != RT_OK) return mr;
       shade<<<d.grid_shade, 128, 0, d.stream>>>(d.sc, level, qin, qout, d.acc, d.c0, d.counters,
-                                                shoot ? d.lvl + (size_t)level * d.tile_cap : nullptr);
+                                                shoot ? d.lvl + (size_t)level * lvl_stride : nullptr);
       plan->launches++;
     }
     int gf = (tg.n_px / 4 + 256) / 256; if (gf > d.grid_fin) gf = d.grid_fin;
     if ((mr = mark(d, 'f')) != RT_OK) return mr;
-    k_finalize<<<gf, 256, 0, d.stream>>>(tg, d.acc, d.c0, dst, shoot ? d.lvl : nullptr, d.tile_cap, g_max_depth);
+    k_finalize<<<gf, 256, 0, d.stream>>>(tg, d.acc, d.c0, dst, shoot ? d.lvl : nullptr, lvl_stride, g_max_depth);
     plan->launches++;
     CK(cudaGetLastError());
   }

@@ -123,6 +123,7 @@ struct HitQueue {
 };
 #define RT_CTL_CURSOR (1 + RT_NCLS)
 #define RT_CTL_STRIDE 16
+static_assert(RT_CTL_CURSOR < RT_CTL_STRIDE, "queue control block too small for RT_NCLS classes + the work cursor");
 
 // Device counters (unsigned long long each).
 enum {

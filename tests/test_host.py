@@ -37,7 +37,7 @@ def test_abi_exports_every_declared_symbol():
     lib = pkg.load_library()
     for sym in declared:
         assert hasattr(lib, sym), f"librt_b200.so does not export {sym}"
-    assert lib.rt_abi_version() == 1
+    assert lib.rt_abi_version() == 2
 
 
 def test_struct_layouts_match_header():

@@ -76,3 +76,26 @@ def test_gpu_shoot_mode_differs_where_the_reference_does(renderer):
     assert np.array_equal(tiled, shoot)
     full = rtlib.oracle_render(MIRRORS, 1500, 1500, mode=1)
     assert np.array_equal(shoot, full)
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_gpu_shoot_mode_deep_bounces_bounded_level_buffer(renderer):
+    """RT_MODE_SHOOT with rt_set_max_depth(50): the per-level buffer is bounded (2 GiB) by shrinking the tile, so a
+    2800 x 1000 frame (2.8 M pixels > the 2 683 904-pixel tile that bound leaves at depth 50) is rendered in two tiles
+    whose level slices are cleared per tile.  Rows on both sides of the tile border against the oracle's shoot() at
+    the same depth."""
+    W, H = 2800, 1000
+    rows = list(range(950, 966)) + [0, 1, 500, 999]              # the border falls in row 958
+    renderer.set_mode(1)
+    renderer.set_max_depth(50)
+    try:
+        renderer.upload(MIRRORS)
+        a, _ = renderer.raycast(W, H)
+        b, _ = renderer.raycast(W, H)                            # second frame: slices hold the first frame's records
+    finally:
+        renderer.set_mode(0)
+        renderer.set_max_depth(7)
+    want = rtlib.oracle_render(MIRRORS, W, H, rows=rows, mode=1, depth=50)
+    assert np.array_equal(a[rows], want)
+    assert np.array_equal(a, b)
