@@ -731,6 +731,13 @@ def main():
             tj = json.load(f)
         ncu_ref = dict(tj.get("ncu") or {}, capture=tj.get("kernel"), file=tj.get("source"),
                        dram_bytes_per_launch_of_that_capture=tj.get("dram_bytes_per_launch"))
+        # the committed capture covers every k_shade launch of one frame of a named configuration: quote its per-launch
+        # mean as `traffic` only when THIS run is that configuration (same workload, frame, tile size, launch count)
+        cfg = tj.get("config") or {}
+        if (world == 1 and cfg.get("workload") == args.workload and cfg.get("width") == W and cfg.get("height") == H
+                and "RT_TILE_PIXELS" not in os.environ and cfg.get("launches_per_frame") == int(agg.launches_shade)
+                and os.environ.get("RT_ACCEL", "0") in ("", "0")):
+            traffic = tj.get("dram_bytes_per_launch")
     except Exception:
         pass
     roof = {"bound": "fp32", "kernel": "k_shade", "achieved": ach, "peak": pk["fp32_tflops"], "unit": "TFLOP/s",

@@ -600,6 +600,9 @@ __device__ __noinline__ void resolve_quadrics(const float (*dsm)[128], const int
                                               const unsigned w0, const unsigned w1, const unsigned w2, const unsigned w3,
                                               const int obj, const bool r_on,
                                               unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand, unsigned &n_setup, unsigned &n_filt) {
+  // no ray left to test (every shadow ray already occluded, or a stand-in lane without a hit point): the quadrics that
+  // passed their ball -- all of them when they have no certified ball -- need no filter set-up for this thread
+  if (!alive) return;
   for (int k = nw - 1; k >= 0; k--)
   for (unsigned sm = k == 0 ? w0 : k == 1 ? w1 : k == 2 ? w2 : w3; sm; sm &= ~(0x80000000u >> __clz(sm))) {
     const int kk = cs + ((nw - 1 - k) << 5) + __clz(sm);
@@ -858,13 +861,17 @@ RT_DEV void scan_spheres_v(const int nrv, const float (*dsm)[128], const int tid
 }
 // Chunks beyond the constant bank (scenes with more than RT_CSPH_CAP spheres): the global-operand loop, one copy per
 // variant but out of line -- it only has to be correct.
+// These variants come in steps of 4 slots while the caller packs and NaN-fills the slots in steps of RT_VSTEP: the
+// slots between the caller's nrv and the compiled width are filled here, or they would carry stale directions (of
+// rays already occluded, or of the previous hit point) through the filter and inflate the survivor lists.
 template <int NRV, int NRMIN>
-__device__ __noinline__ void scan_spheres_g(const int nrv, const float (*dsm)[128], const int tid, const v3 P,
+__device__ __noinline__ void scan_spheres_g(const int nrv, float (*dsm)[128], const int tid, const v3 P,
                                             const DevScene &sc, const int cs, const int n, const int obj, const bool r_on,
                                             unsigned &alive, float &best_t, int &best_idx, unsigned &n_cand) {
   if constexpr (NRV - 4 >= NRMIN) {
     if (nrv <= NRV - 4) { scan_spheres_g<NRV - 4, NRMIN>(nrv, dsm, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand); return; }
   }
+  for (int j = nrv; j < NRV; j++) { dsm[3 * j][tid] = RT_NAN; dsm[3 * j + 1][tid] = RT_NAN; dsm[3 * j + 2][tid] = RT_NAN; }
   scan_chunk_g<NRV>(dsm, tid, P, sc, cs, n, obj, r_on, alive, best_t, best_idx, n_cand);
 }
 template <int NRV, int NRMIN>

@@ -181,6 +181,22 @@ def test_zoo_scenes(renderer, name):
         assert int(st.rays_shadow) == ct.rays_shadow and int(st.rays_reflection) == ct.rays_reflection
 
 
+def test_zoo_spots_cuda_pow_against_glibc_pow(renderer):
+    """Spot lights with non-integer angular-a0 (0.01 .. 63.5): the only libm call of the CUDA path that is not the
+    reference's own routine (CUDA pow vs glibc pow, rt_math.cuh pow_a0 vs C/raycast.c:695).  Golden frame rendered by
+    the reference itself; larger frames against the oracle port (which calls glibc pow)."""
+    path = os.path.join(rtlib.SCENES, "zoo_spots.scene")
+    gold = np.load(os.path.join(rtlib.GOLDEN, "zoo_spots.npz"))["zoo_spots"]
+    renderer.upload(path)
+    img, _ = renderer.raycast(gold.shape[1], gold.shape[0])
+    rep = rtlib.compare(img, gold)
+    assert rep["identical_frac"] == 1.0, rep
+    for W, H in ((640, 480), (1201, 907)):
+        img, _ = renderer.raycast(W, H)
+        rep = rtlib.compare(img, rtlib.oracle_render(path, W, H))
+        assert rep["identical_frac"] == 1.0, (W, H, rep)
+
+
 def _many_spheres_scene(path, n, seed=7):
     """n small spheres (some mirrors) + a floor + 3 lights: more spheres than the constant bank of the scan holds."""
     rng = np.random.RandomState(seed)

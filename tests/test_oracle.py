@@ -111,3 +111,11 @@ def test_oracle_matches_golden_zoo(name):
     img = rtlib.oracle_render(os.path.join(rtlib.SCENES, f"{name}.scene"), gold.shape[1], gold.shape[0])
     rep = rtlib.compare(img, gold)
     assert rep["identical_frac"] == 1.0, rep
+
+
+def test_oracle_matches_golden_zoo_spots():
+    """12 spot lights with non-integer angular-a0 (glibc pow in the reference, C/raycast.c:695): restatement vs the
+    reference's own render (tests/golden/make_zoo_spots.py)."""
+    gold = np.load(os.path.join(rtlib.GOLDEN, "zoo_spots.npz"))["zoo_spots"]
+    img = rtlib.oracle_render(os.path.join(rtlib.SCENES, "zoo_spots.scene"), gold.shape[1], gold.shape[0])
+    assert rtlib.compare(img, gold)["identical_frac"] == 1.0
